@@ -1,0 +1,215 @@
+"""oracle/bindings.py — TEST INFRASTRUCTURE, not product code.
+
+ctypes bindings for the two CPU checkers:
+  * ``Oracle``    -> oracle/liboracle.so       (plain-C restatement, oracle/nbody_oracle.c)
+  * ``Reference`` -> oracle/_ref/libnbref.so   (the unmodified reference, oracle/ref_shim.cpp)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+import this module. The product package never does.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libnbref.so")
+
+_dp = C.POINTER(C.c_double)
+_fp = C.POINTER(C.c_float)
+_bp = C.POINTER(C.c_uint8)
+
+
+def _d(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _f(a):
+    return None if a is None else a.ctypes.data_as(_fp)
+
+
+def _b(a):
+    return None if a is None else a.ctypes.data_as(_bp)
+
+
+class OrcConfig(C.Structure):
+    _fields_ = [("g", C.c_double), ("softening", C.c_float), ("max_speed", C.c_float),
+                ("integrator", C.c_int), ("max_substep", C.c_float), ("max_substeps_per_frame", C.c_int)]
+
+
+# Reference defaults (src/core/Constants.hpp:86-100, src/core/Config.hpp:25).
+DEFAULTS = dict(g=6.67430e-11, softening=4.0, max_speed=0.0, integrator=1, fixed_dt=float(np.float32(1.0) / np.float32(120)),
+                time_scale=1e6, max_substep=1.0e9, max_substeps_per_frame=200)
+
+
+def make_config(**kw):
+    d = dict(DEFAULTS)
+    d.update(kw)
+    return OrcConfig(d["g"], d["softening"], d["max_speed"], d["integrator"], d["max_substep"],
+                     d["max_substeps_per_frame"])
+
+
+def dt_eff(fixed_dt=DEFAULTS["fixed_dt"], time_scale=DEFAULTS["time_scale"]):
+    """dtEff as the integrate system computes it in float (Physics.hpp:54-55)."""
+    return float(np.float32(fixed_dt) * max(np.float32(0.0), np.float32(time_scale)))
+
+
+class Oracle:
+    """Plain-C restatement on flat numpy arrays."""
+
+    def __init__(self, path=ORACLE_SO):
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.orc_substep_plan.restype = C.c_int
+        L.orc_substep_plan.argtypes = [C.c_float, C.c_float, C.c_int, _fp]
+        L.orc_compute_diagnostics.restype = C.c_int
+        L.orc_compute_diagnostics3.restype = C.c_int
+
+    @staticmethod
+    def _dim(pos):
+        return pos.shape[1]
+
+    def compute_gravity(self, pos, vel, mass, pinned=None, g=DEFAULTS["g"], softening=DEFAULTS["softening"], acc=None):
+        n, dim = pos.shape
+        pos = np.ascontiguousarray(pos, np.float64)
+        vel = np.ascontiguousarray(vel, np.float64)
+        mass = np.ascontiguousarray(mass, np.float32)
+        pinned = None if pinned is None else np.ascontiguousarray(pinned, np.uint8)
+        acc = np.zeros((n, dim)) if acc is None else np.ascontiguousarray(acc, np.float64)
+        fn = self.lib.orc_compute_gravity if dim == 2 else self.lib.orc_compute_gravity3
+        fn(C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned), C.c_double(g), C.c_float(softening), _d(acc))
+        return acc
+
+    def substep_plan(self, dt, max_substep=DEFAULTS["max_substep"], max_substeps=DEFAULTS["max_substeps_per_frame"]):
+        out = C.c_float()
+        n = self.lib.orc_substep_plan(C.c_float(dt), C.c_float(max_substep), C.c_int(max_substeps), C.byref(out))
+        return n, out.value
+
+    def integrate(self, pos, vel, acc, acc_prev, mass, pinned, cfg, dt):
+        """In place on float64 C-contiguous arrays."""
+        n, dim = pos.shape
+        fn = self.lib.orc_integrate if dim == 2 else self.lib.orc_integrate3
+        fn(C.c_int64(n), _d(pos), _d(vel), _d(acc), _d(acc_prev), _f(mass), _b(pinned), C.byref(cfg), C.c_float(dt))
+
+    def physics_frames(self, pos, vel, acc, acc_prev, mass, pinned, cfg, dt, n_frames=1):
+        n, dim = pos.shape
+        fn = self.lib.orc_physics_frames if dim == 2 else self.lib.orc_physics_frames3
+        fn(C.c_int64(n), _d(pos), _d(vel), _d(acc), _d(acc_prev), _f(mass), _b(pinned), C.byref(cfg),
+           C.c_float(dt), C.c_int64(n_frames))
+
+    def compute_diagnostics(self, pos, vel, mass, g=DEFAULTS["g"], softening=DEFAULTS["softening"]):
+        n, dim = pos.shape
+        pos = np.ascontiguousarray(pos, np.float64)
+        vel = np.ascontiguousarray(vel, np.float64)
+        mass = np.ascontiguousarray(mass, np.float32)
+        eps2 = float(np.float64(np.float32(softening)) * np.float64(np.float32(softening)))
+        out = np.zeros(8 if dim == 2 else 10)
+        fn = self.lib.orc_compute_diagnostics if dim == 2 else self.lib.orc_compute_diagnostics3
+        ok = fn(C.c_int64(n), _d(pos), _d(vel), _f(mass), C.c_double(g), C.c_double(eps2), _d(out))
+        return out, bool(ok)
+
+    def zero_net_momentum(self, vel, mass, pinned=None):
+        n = vel.shape[0]
+        self.lib.orc_zero_net_momentum(C.c_int64(n), _d(vel), _f(mass), _b(pinned))
+
+    def seed_three_body(self, g=DEFAULTS["g"]):
+        pos = np.zeros((3, 2))
+        vel = np.zeros((3, 2))
+        mass = np.zeros(3, np.float32)
+        pinned = np.zeros(3, np.uint8)
+        self.lib.orc_seed_three_body(C.c_double(g), _d(pos), _d(vel), _f(mass), _b(pinned))
+        return pos, vel, mass, pinned
+
+
+class Reference:
+    """The unmodified reference physics (2-D), through oracle/ref_shim.cpp."""
+
+    def __init__(self, path=REF_SO):
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.ref_world_create.restype = C.c_void_p
+        L.ref_reset_scenario.restype = C.c_int64
+        L.ref_num_bodies.restype = C.c_int64
+        L.ref_dt_eff.restype = C.c_float
+        L.ref_compute_diagnostics.restype = C.c_int
+        L.ref_read_frame_diagnostics.restype = C.c_int
+        L.ref_paused.restype = C.c_int
+        self.h = C.c_void_p(L.ref_world_create())
+
+    def close(self):
+        if self.h:
+            self.lib.ref_world_destroy(self.h)
+            self.h = None
+
+    def set_config(self, **kw):
+        d = dict(DEFAULTS)
+        d.update(kw)
+        self.lib.ref_set_config(self.h, C.c_double(d["g"]), C.c_float(d["softening"]), C.c_float(d["max_speed"]),
+                                C.c_int(d["integrator"]), C.c_float(d["fixed_dt"]), C.c_float(d["time_scale"]),
+                                C.c_float(d["max_substep"]), C.c_int(d["max_substeps_per_frame"]))
+
+    def defaults(self):
+        g = C.c_double()
+        s, ms, fd, ts, sub = C.c_float(), C.c_float(), C.c_float(), C.c_float(), C.c_float()
+        it, nsub = C.c_int(), C.c_int()
+        self.lib.ref_get_defaults(C.byref(g), C.byref(s), C.byref(ms), C.byref(it), C.byref(fd), C.byref(ts),
+                                  C.byref(sub), C.byref(nsub))
+        return dict(g=g.value, softening=s.value, max_speed=ms.value, integrator=it.value, fixed_dt=fd.value,
+                    time_scale=ts.value, max_substep=sub.value, max_substeps_per_frame=nsub.value)
+
+    def load_bodies(self, pos, vel, mass, pinned=None):
+        n = pos.shape[0]
+        pos = np.ascontiguousarray(pos, np.float64)
+        vel = np.ascontiguousarray(vel, np.float64)
+        mass = np.ascontiguousarray(mass, np.float32)
+        pinned = None if pinned is None else np.ascontiguousarray(pinned, np.uint8)
+        self.lib.ref_load_bodies(self.h, C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned))
+
+    def reset_scenario(self):
+        return self.lib.ref_reset_scenario(self.h)
+
+    def num_bodies(self):
+        return self.lib.ref_num_bodies(self.h)
+
+    def read_bodies(self):
+        n = self.num_bodies()
+        pos, vel, acc = np.zeros((n, 2)), np.zeros((n, 2)), np.zeros((n, 2))
+        mass, pinned = np.zeros(n, np.float32), np.zeros(n, np.uint8)
+        self.lib.ref_read_bodies(self.h, _d(pos), _d(vel), _d(acc), _f(mass), _b(pinned))
+        return pos, vel, acc, mass, pinned
+
+    def zero_net_momentum(self):
+        self.lib.ref_zero_net_momentum(self.h)
+
+    def compute_gravity(self):
+        self.lib.ref_compute_gravity(self.h)
+
+    def integrate(self, dt):
+        self.lib.ref_integrate(self.h, C.c_float(dt))
+
+    def dt_eff(self):
+        return self.lib.ref_dt_eff(self.h)
+
+    def physics_frame(self):
+        self.lib.ref_physics_frame(self.h)
+
+    def progress(self):
+        self.lib.ref_progress(self.h)
+
+    def paused(self):
+        return bool(self.lib.ref_paused(self.h))
+
+    def compute_diagnostics(self):
+        out = np.zeros(8)
+        ok = self.lib.ref_compute_diagnostics(self.h, _d(out))
+        return out, bool(ok)
+
+    def frame_diagnostics(self):
+        out = np.zeros(8)
+        ok = self.lib.ref_read_frame_diagnostics(self.h, _d(out))
+        return out, ok
+
+
+def have_reference():
+    return os.path.exists(REF_SO)
