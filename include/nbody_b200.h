@@ -1,0 +1,181 @@
+/* include/nbody_b200.h — C-ABI of the B200-native physics step.
+ *
+ * Drop-in boundary for the hot path of tr0yspradling/raylib-nbody: the three private
+ * statics its flecs systems call (src/systems/Physics.hpp:32-64). The reference has no
+ * FFI of its own; the seam is the gather/scatter code inside those statics
+ * (Physics.hpp:197-205, :120-121, :260), and these entry points are what a maintainer
+ * binds in their place (INTEGRATION.md shows the patch to register_systems).
+ *
+ * Conventions
+ *   - plain C, POD only, no exceptions across the boundary; every call returns an
+ *     nb_status (0 = ok) and nb_last_error() gives the message for the calling thread.
+ *   - host arrays are borrowed for the duration of a call; device state is owned by the
+ *     opaque nb_ctx. Body identity = array index in upload order.
+ *   - 2-D entry points use the reference's layouts exactly: interleaved {x,y} doubles
+ *     (DVec2, src/core/Math.hpp:6-9), f32 mass (Components.hpp:22-24), u8 pinned
+ *     (Components.hpp:36-38). The *3 variants carry {x,y,z}; a 2-D upload is the 3-D
+ *     state with z == 0 (every z term is then exactly zero).
+ *   - there is NO CPU fallback: without a CUDA device nb_create fails with
+ *     NB_ERR_NO_DEVICE and nothing else can be called.
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_ABI_VERSION 1
+
+typedef enum nb_status {
+    NB_OK = 0,
+    NB_ERR_INVALID = 1,    /* bad argument / call order */
+    NB_ERR_NO_DEVICE = 2,  /* no usable CUDA device (never falls back to the CPU) */
+    NB_ERR_CUDA = 3,       /* CUDA runtime failure, message in nb_last_error() */
+    NB_ERR_NCCL = 4,       /* NCCL failure or NCCL not loadable */
+    NB_ERR_ALLOC = 5
+} nb_status;
+
+typedef struct nb_ctx nb_ctx;
+
+/* Physics fields of the reference's Config singleton (src/core/Config.hpp:13-29,
+ * defaults src/core/Constants.hpp:86-100). bh_threshold/bh_theta are absent on purpose:
+ * this library always evaluates the direct sum (Physics.hpp:231-258). */
+typedef struct nb_config {
+    double g;                   /* Config::g                      6.6743e-11 */
+    float softening;            /* Config::softening (epsilon, m) 4.0        */
+    float max_speed;            /* Config::max_speed, 0 = off     0.0        */
+    int32_t integrator;         /* 0 semi-implicit Euler, 1 velocity Verlet (default 1) */
+    float max_substep;          /* Config::max_substep            1e9        */
+    int32_t max_substeps_per_frame; /* Config::max_substeps_per_frame 200    */
+} nb_config;
+
+/* Arithmetic of the force evaluation (nb_set_precision).
+ *   FP32       the hot path: FP32 pair terms, FP64 accumulation across 32-source chunks and
+ *              FP64 integrator state; per-body acceleration within 1e-5 of the reference.
+ *   FP64_EXACT the reference's own FP64 operation order (Physics.hpp:237-254), bit-identical
+ *              accelerations and trajectories; about 1/15 of the FP32 throughput.
+ *   AUTO       FP64_EXACT for worlds of at most NB_EXACT_AUTO_MAX bodies (where the force
+ *              pass is launch-bound anyway and configurations such as the three-body seed are
+ *              dynamically unstable), FP32 above. Default. */
+#define NB_PRECISION_AUTO 0
+#define NB_PRECISION_FP32 1
+#define NB_PRECISION_FP64_EXACT 2
+#define NB_EXACT_AUTO_MAX 512
+
+#define NB_INTEGRATOR_EULER 0
+#define NB_INTEGRATOR_VERLET 1
+
+/* Physics::Diagnostics (Physics.hpp:22-30) widened to three components; for 2-D state
+ * the [2] entries are 0. */
+typedef struct nb_diag {
+    double kinetic;
+    double potential;
+    double energy;
+    double momentum[3];
+    double com[3];
+    double total_mass;
+    int32_t ok; /* Diagnostics::ok: 0 when any sum is non-finite (the shim then sets cfg->paused) */
+    int32_t _pad;
+} nb_diag;
+
+/* ---- lifetime -------------------------------------------------------------------- */
+
+/* One context on CUDA device `device`. */
+int nb_create(int device, nb_ctx** out);
+
+/* Target-partitioned context: rank `rank` of `world` owns bodies [lo,hi) of every upload
+ * (nb_local_range) and exchanges packed positions with its peers through NCCL once per
+ * force evaluation. `nccl_unique_id` is the 128-byte id from nb_comm_unique_id() on rank 0,
+ * distributed by the caller (torch.distributed / MPI / a file). Collective over all ranks. */
+int nb_comm_unique_id(void* out_id_128);
+int nb_create_sharded(int device, int rank, int world, const void* nccl_unique_id, nb_ctx** out);
+
+void nb_destroy(nb_ctx* ctx);
+const char* nb_last_error(void);
+int nb_abi_version(void);
+
+/* ---- configuration ---------------------------------------------------------------- */
+
+int nb_default_config(nb_config* out);            /* Constants.hpp:86-100 + Config.hpp:25 */
+int nb_set_config(nb_ctx* ctx, const nb_config* cfg);
+int nb_get_config(nb_ctx* ctx, nb_config* out);
+int nb_set_precision(nb_ctx* ctx, int precision); /* NB_PRECISION_*; single-GPU contexts only for FP64_EXACT */
+
+/* ---- state ------------------------------------------------------------------------ */
+
+/* Replaces all bodies (the gather of Physics.hpp:197-205). `pinned` may be NULL.
+ * Accelerations start at zero like freshly created entities (Physics.hpp:97-98); the next
+ * step evaluates a(x) first, as the gravity system does. Sharded: every rank passes the
+ * same full arrays. */
+int nb_upload(nb_ctx* ctx, int64_t n, const double* pos_xy, const double* vel_xy, const float* mass,
+              const uint8_t* pinned);
+int nb_upload3(nb_ctx* ctx, int64_t n, const double* pos_xyz, const double* vel_xyz, const float* mass,
+               const uint8_t* pinned);
+
+/* Scatter back (Physics.hpp:260 and the in-place writes of :276-323). Any pointer may be
+ * NULL. Arrays are sized for all n bodies; a sharded context fills rows [lo,hi) only. */
+int nb_download(nb_ctx* ctx, double* pos_xy, double* vel_xy, double* acc_xy);
+int nb_download3(nb_ctx* ctx, double* pos_xyz, double* vel_xyz, double* acc_xyz);
+
+int64_t nb_num_bodies(nb_ctx* ctx);
+int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);
+
+/* ---- the hot path ----------------------------------------------------------------- */
+
+/* Physics::compute_gravity (Physics.hpp:183-261): Acceleration <- a(x) by direct sum.
+ * Bodies with non-finite x/v or m <= 0 neither attract nor receive a new acceleration;
+ * pinned bodies attract and get a = 0. */
+int nb_compute_gravity(nb_ctx* ctx);
+
+/* Physics::integrate (Physics.hpp:263-327) with the reference's substep plan. Requires
+ * Acceleration == a(x) on entry, i.e. nb_compute_gravity ran since the last upload, exactly
+ * as sys2 runs before sys3. */
+int nb_integrate(nb_ctx* ctx, float dt);
+
+/* n_frames x (gravity system + integrate system), Physics.hpp:45-57, with dt_eff =
+ * baseDt * max(0, time_scale) computed by the caller (Physics.hpp:54-55). This is the fused
+ * path: one force kernel per substep with the kick/drift in its epilogue; the gravity
+ * system's evaluation is skipped when Acceleration already equals a(x). Asynchronous. */
+int nb_step(nb_ctx* ctx, float dt_eff, int64_t n_frames);
+
+/* Same, additionally accumulating the potential in the force pass so nb_step_diagnostics
+ * returns the energy/momentum of the state at the end of the call without another O(N^2)
+ * pass. For Euler it describes the state the last force evaluation saw (frame start), as
+ * the reference's diagnostics do (Physics.hpp:34-42). */
+int nb_step_with_diagnostics(nb_ctx* ctx, float dt_eff, int64_t n_frames);
+int nb_step_diagnostics(nb_ctx* ctx, nb_diag* out);
+
+/* Physics::compute_diagnostics (Physics.hpp:117-177) over ALL bodies, unfiltered.
+ * Sharded: collective, every rank receives the global values. Synchronises. */
+int nb_compute_diagnostics(nb_ctx* ctx, nb_diag* out);
+
+/* Physics::zero_net_momentum (Physics.hpp:66-85). */
+int nb_zero_net_momentum(nb_ctx* ctx);
+
+/* Substep plan of Physics.hpp:268-271 (float arithmetic). Host-only helper. */
+int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub);
+
+/* Physics::reset_scenario (Physics.hpp:87-115): uploads the three-body seed. */
+int nb_reset_scenario(nb_ctx* ctx);
+
+/* ---- synchronisation and measurement ---------------------------------------------- */
+
+int nb_synchronize(nb_ctx* ctx);
+/* CUDA events on the library's own stream around whatever is enqueued between them. */
+int nb_timer_begin(nb_ctx* ctx);
+int nb_timer_end(nb_ctx* ctx, float* elapsed_ms); /* synchronises */
+/* Kernels launched / force evaluations / body-body interactions since creation. */
+int nb_counters(nb_ctx* ctx, int64_t* kernel_launches, int64_t* force_evals, double* interactions);
+/* Device-time of the force kernels alone since the last call (events around every force
+ * launch when profiling is on). */
+int nb_profile_forces(nb_ctx* ctx, int enable);
+int nb_profile_read(nb_ctx* ctx, int64_t* n_launches, double* total_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

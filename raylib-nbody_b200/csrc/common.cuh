@@ -1,0 +1,109 @@
+// common.cuh — shared device/host definitions for the B200 physics step.
+//
+// Data layout in HBM (all owned by nb_ctx, see nbody_b200.cu):
+//   state   : SoA FP64, three components each: x[3][n], v[3][n], a[3][n], a0[3][n]
+//             (the reference's Position/Velocity/Acceleration/PrevAcceleration DVec2
+//              components, src/components/Components.hpp:10-21, widened with z)
+//   mass    : f32[n] (Components.hpp:22-24), pinned : u8[n] (Components.hpp:36-38)
+//   j-stream: FP32 "pair-SoA" packed sources, 32 B per body PAIR:
+//             {x0,x1,y0,y1,z0,z1,m0,m1}; two generations (cur/next) because the fused
+//             epilogue writes step k+1's stream while other CTAs still read step k's.
+//             Positions are scaled by an exact power of two 2^-e (so a float-representable
+//             input is carried unchanged) and masses by 2^-q; G, 2^q and 2^-2e are applied
+//             in FP64 in the epilogue, never rounded to FP32.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nb {
+
+constexpr int kTileBodies = 512;          // j-bodies per shared-memory stage (16 KB)
+constexpr int kStages = 2;                // TMA bulk-copy ring depth
+constexpr int kFlushChunk = 32;           // FP32 partial sums are folded into FP64 every 32 sources
+constexpr int kExtentSlots = 4;           // rotating max|x| slots, see scale_for()
+constexpr int kHeadroomLog2 = 17;         // scaled |x| < 2^17 when packed; r^6 stays finite up to 2^19
+constexpr int kMaxSegments = 16;          // j-split factor upper bound
+constexpr int kDiagValues = 12;           // KE, PE, Px,Py,Pz, Cx,Cy,Cz, M, nonfinite, pad, pad
+
+// Power-of-two scales for one generation of the j-stream.
+struct Scale {
+    double inv_len;   // 2^-e : physical length -> packed units
+    double acc_unit;  // G * 2^q * 2^-2e : packed acceleration sum -> m/s^2
+    double pot_unit;  // 2^q * 2^-e : packed potential sum -> kg/m
+    float eps2;       // softening^2 in packed units, floored so r^6 never underflows
+};
+
+__host__ __device__ inline double pow2d(int k) {
+    // exact 2^k for k in the normal double range
+    union { uint64_t u; double d; } c;
+    c.u = (uint64_t)(k + 1023) << 52;
+    return c.d;
+}
+
+// extent_bits: IEEE bits of max|coordinate| over live bodies (a non-negative float).
+__host__ __device__ inline int extent_exponent(unsigned int extent_bits) {
+    int ex = (int)((extent_bits >> 23) & 0xffu) - 126;  // value < 2^ex for normal floats
+    if (ex < -60) ex = -60;                            // all bodies at (or next to) the origin
+    if (ex > 100) ex = 100;
+    return ex;
+}
+
+__host__ __device__ inline Scale scale_for(unsigned int extent_bits, int mass_exp, double g, float softening) {
+    const int e = extent_exponent(extent_bits) - kHeadroomLog2;  // length unit 2^e
+    Scale s;
+    s.inv_len = pow2d(-e);
+    s.acc_unit = g * pow2d(mass_exp) * s.inv_len * s.inv_len;
+    s.pot_unit = pow2d(mass_exp) * s.inv_len;
+    const double eps = (double)softening * s.inv_len;
+    double eps2 = eps * eps;
+    const double floor2 = 4.547473508864641e-13;  // 2^-41: (2^-41)^3 = 2^-123 > FLT_MIN
+    if (!(eps2 >= floor2)) eps2 = floor2;
+    if (eps2 > 1.0e30) eps2 = 1.0e30;
+    s.eps2 = (float)eps2;
+    return s;
+}
+
+// Epilogue modes of the force kernel.
+enum Mode : int {
+    kForceOnly = 0,     // Physics::compute_gravity, Physics.hpp:183-261
+    kVerletKick = 1,    // ... + kick of Physics.hpp:309-323
+    kVerletKickDrift = 2,  // ... + drift of the NEXT substep (Physics.hpp:297-304) and its pack
+    kEuler = 3,         // ... + kick/drift of Physics.hpp:276-290 and the next pack
+    kPartialOnly = 4    // no epilogue: leave the FP64 sums in `part` slot 0 for a later launch
+};
+
+struct StepParams {
+    double* x[3];
+    double* v[3];
+    double* a[3];
+    double* a0[3];
+    const float* mass;
+    const uint8_t* pinned;
+    uint8_t* live;              // gather filter of Physics.hpp:198-199, per body
+    const float* pk_cur;        // pair-SoA j-stream being read (generation `gen`)
+    float* pk_next;             // generation gen+1, written by the epilogue
+    unsigned int* extent;       // kExtentSlots rotating slots of float bits
+    double* part;               // [1 + nseg][4][i_cap] FP64 partial sums: slot 0 carries sums between two
+                                // launches (local / remote sources), slots 1.. the source segments
+    unsigned int* tile_counter; // [n_itiles] arrival counters (only nseg > 1)
+    double* diag_part;          // [n_itiles][kDiagValues] per-CTA diagnostics partials
+    long long n;                // bodies
+    long long n_tiles;          // j-stream length in tiles of kTileBodies (padded with m = 0)
+    long long i_lo, i_hi;       // target range owned by this rank
+    long long i_cap;            // row stride of `part`
+    long long j_tile_lo, j_tile_hi;  // LOGICAL source tiles this launch covers, split over nseg CTAs
+    long long hole_lo, hole_len;     // logical tile t >= hole_lo maps to physical tile t + hole_len
+                                     // (the remote-sources launch skips the rank's own tiles this way)
+    int nseg;
+    int gen;
+    int mode;
+    int accumulate;             // 1: add `part` slot 0 (an earlier launch's sums) before the epilogue
+    int mass_exp;
+    float softening;
+    float max_speed;
+    double g;
+    double dt;                  // (double)dtSub
+    double half_dt2;            // 0.5 * dt * dt, Physics.hpp:300
+};
+
+}  // namespace nb

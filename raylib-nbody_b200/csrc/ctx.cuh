@@ -1,0 +1,112 @@
+// ctx.cuh — the context behind the opaque nb_ctx handle: device buffers, streams, the
+// force-launch plan, and (for target-partitioned contexts) the NCCL communicator.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/nbody_b200.h"
+#include "common.cuh"
+#include "state.cuh"
+
+namespace nb {
+
+// NCCL is resolved at run time (dlopen) so single-GPU users never need it on the loader path.
+struct NcclApi;
+
+// How one force launch is cut into CTAs.
+struct LaunchPlan {
+    int variant = 0;   // index into the kernel table (R, packed)
+    int r = 4;         // targets per thread
+    int nseg = 1;      // source segments
+    long long n_itiles = 0;
+    int ctas_per_sm = 1;
+};
+
+struct Variant {
+    int nt, r, packed;
+};
+
+}  // namespace nb
+
+struct nb_ctx {
+    int device = 0;
+    int rank = 0, world = 1;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;       // all kernels
+    cudaStream_t comm_stream = nullptr;  // NCCL exchange, high priority
+    cudaEvent_t ev_timer0 = nullptr, ev_timer1 = nullptr;
+    cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr;
+
+    nb_config cfg;
+    int dim = 2;  // 2: reference layout uploads, 3: xyz uploads
+    int precision = NB_PRECISION_AUTO;
+    bool step_diag_exact = false;  // nb_step_diagnostics recomputes (exact path has no fused potential)
+
+    // ---- bodies ----
+    long long n = 0;          // all bodies
+    long long cap = 0;        // allocated rows
+    long long lo = 0, hi = 0; // rows owned by this rank
+    long long n_tiles = 0;    // j-stream tiles (padded to world * tiles_per_rank)
+    long long tiles_per_rank = 0;
+    double* state = nullptr;  // 12 * cap doubles: x[3], v[3], a[3], a0[3]
+    float* mass = nullptr;
+    uint8_t* pinned = nullptr;
+    uint8_t* live = nullptr;
+    float* pk[2] = {nullptr, nullptr};  // pair-SoA j-stream generations
+    unsigned int* extent = nullptr;     // kExtentSlots + 4 slots
+    double* part = nullptr;             // FP64 partial sums, (1 + part_slots) * 4 * i_cap
+    long long i_cap = 0;
+    int part_slots = 0;
+    unsigned int* tile_counter = nullptr;
+    long long counter_cap = 0;
+    double* diag_part = nullptr;        // per-CTA diagnostics partials
+    long long diag_part_rows = 0;
+    double* totals = nullptr;           // device scratch for fixed-order final sums (64 doubles)
+    double* h_totals = nullptr;         // pinned host mirror
+    float4* dpk = nullptr;              // stand-alone diagnostics pack
+    void* staging = nullptr;            // device staging for AoS uploads/downloads
+    size_t staging_bytes = 0;
+
+    int gen = 0;               // generation of pk[gen & 1]
+    int mass_exp = 0;          // masses are packed as m * 2^-mass_exp
+    bool acc_valid = false;    // Acceleration == a(x) for the current positions
+    bool packed_valid = false; // pk[gen & 1] matches the current positions
+    bool step_diag_valid = false;
+    long long step_diag_rows = 0;
+
+    // ---- launch plans ----
+    nb::LaunchPlan plans[3][2];  // [all | own sources | remote sources][without / with potential]
+    int forced_r = 0, forced_packed = -1, forced_nseg = 0;
+
+    // ---- measurement ----
+    long long kernel_launches = 0;
+    long long force_evals = 0;
+    double interactions = 0.0;
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_events;  // pairs
+    size_t prof_used = 0;
+
+    // ---- NCCL ----
+    void* nccl_comm = nullptr;
+
+    double* sx(int c) const { return state + (long long)c * cap; }
+    nb::StateView view() const {
+        nb::StateView s;
+        for (int k = 0; k < 3; ++k) {
+            s.x[k] = sx(k);
+            s.v[k] = sx(3 + k);
+            s.a[k] = sx(6 + k);
+            s.a0[k] = sx(9 + k);
+        }
+        s.mass = mass;
+        s.pinned = pinned;
+        s.live = live;
+        s.n = n;
+        s.lo = lo;
+        s.hi = hi;
+        return s;
+    }
+};

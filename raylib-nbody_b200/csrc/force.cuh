@@ -1,0 +1,140 @@
+// force.cuh — the hot kernel: j-tiled direct-sum softened gravity with the integrator
+// kick/drift (and the next step's FP32 pack) fused into its epilogue.
+//
+// Replaces the reference's hot loop A, src/systems/Physics.hpp:231-258 (direct all-pairs
+// branch of compute_gravity) and the per-body loops of integrate(), Physics.hpp:276-290
+// (semi-implicit Euler) and :297-323 (velocity Verlet). It is a full N x N target-major
+// sweep (each target sums all sources in ascending index), not the reference's triangular
+// pair loop, so no atomics and a fixed, reproducible summation order.
+//
+// Per interaction (3-D): 3 FADD, 3 FFMA (r^2 seeded with eps^2), 2 FMUL (r^6), 1 MUFU.RSQ
+// (r^-3 directly: one rsqrt error instead of three), 1 FMUL (m r^-3), 3 FFMA  = 12 FP32-pipe
+// ops + 1 SFU op = the conventional 20 FLOPs. With PACKED the 12 FP32 ops are issued as 6
+// two-wide FFMA2/FADD2/FMUL2 on a pair of sources. Compute-bound on the FP32 pipe; HBM sees
+// the j-stream once per CTA through L2 (TMA bulk copies into a shared-memory ring).
+#pragma once
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace nb {
+
+// One target body's running sums: FP32 inside a flush chunk, FP64 across chunks.
+template <bool PACKED, bool POT>
+struct Target;
+
+// ---- scalar FP32 variant ------------------------------------------------------------
+template <bool POT>
+struct Target<false, POT> {
+    float xi, yi, zi;
+    float ax, ay, az, ph;
+    __device__ __forceinline__ void init(float x, float y, float z) {
+        xi = x; yi = y; zi = z;
+        ax = ay = az = ph = 0.f;
+    }
+    // rec: one pair record {x0,x1,y0,y1 | z0,z1,m0,m1}; m0/m1 may be masked by the caller
+    __device__ __forceinline__ void interact(const float4& A, const float4& B, float m0, float m1, float eps2) {
+        one(A.x, A.z, B.x, m0, eps2);
+        one(A.y, A.w, B.y, m1, eps2);
+    }
+    __device__ __forceinline__ void one(float xj, float yj, float zj, float mj, float eps2) {
+        const float dx = xj - xi, dy = yj - yi, dz = zj - zi;
+        float r2 = __fmaf_rn(dx, dx, eps2);
+        r2 = __fmaf_rn(dy, dy, r2);
+        r2 = __fmaf_rn(dz, dz, r2);
+        const float r6 = (r2 * r2) * r2;
+        const float w = rsqrt_fast(r6);  // r^-3
+        const float s = mj * w;
+        ax = __fmaf_rn(s, dx, ax);
+        ay = __fmaf_rn(s, dy, ay);
+        az = __fmaf_rn(s, dz, az);
+        if (POT) ph = __fmaf_rn(mj, w * r2, ph);  // m / r
+    }
+    __device__ __forceinline__ void flush(double& Ax, double& Ay, double& Az, double& Ph) {
+        Ax += (double)ax; Ay += (double)ay; Az += (double)az;
+        ax = ay = az = 0.f;
+        if (POT) { Ph += (double)ph; ph = 0.f; }
+    }
+};
+
+// ---- packed f32x2 variant (two sources per instruction) -------------------------------
+template <bool POT>
+struct Target<true, POT> {
+    f2 nxi, nyi, nzi;  // {-x,-x} ... so dx = xj + (-xi) is one FADD2
+    f2 ax, ay, az, ph;
+    __device__ __forceinline__ void init(float x, float y, float z) {
+        nxi = f2_make(-x, -x); nyi = f2_make(-y, -y); nzi = f2_make(-z, -z);
+        ax = ay = az = ph = f2_make(0.f, 0.f);
+    }
+    __device__ __forceinline__ void interact(f2 xj, f2 yj, f2 zj, f2 mj, f2 eps2) {
+        const f2 dx = f2_add(xj, nxi), dy = f2_add(yj, nyi), dz = f2_add(zj, nzi);
+        f2 r2 = f2_fma(dx, dx, eps2);
+        r2 = f2_fma(dy, dy, r2);
+        r2 = f2_fma(dz, dz, r2);
+        const f2 r6 = f2_mul(f2_mul(r2, r2), r2);
+        float lo, hi;
+        f2_split(r6, lo, hi);
+        const f2 w = f2_make(rsqrt_fast(lo), rsqrt_fast(hi));
+        const f2 s = f2_mul(mj, w);
+        ax = f2_fma(s, dx, ax);
+        ay = f2_fma(s, dy, ay);
+        az = f2_fma(s, dz, az);
+        if (POT) ph = f2_fma(mj, f2_mul(w, r2), ph);
+    }
+    // The even/odd-source halves are added in FP32 first: one commutative, sign-symmetric
+    // rounding, so mirror-symmetric configurations (the reference's three-body seed,
+    // Physics.hpp:87-115) keep exactly mirrored sums whatever slot a source landed in.
+    __device__ __forceinline__ void flush(double& Ax, double& Ay, double& Az, double& Ph) {
+        float lo, hi;
+        f2_split(ax, lo, hi); Ax += (double)(lo + hi);
+        f2_split(ay, lo, hi); Ay += (double)(lo + hi);
+        f2_split(az, lo, hi); Az += (double)(lo + hi);
+        ax = ay = az = f2_make(0.f, 0.f);
+        if (POT) { f2_split(ph, lo, hi); Ph += (double)(lo + hi); ph = f2_make(0.f, 0.f); }
+    }
+};
+
+// One flush chunk (kFlushChunk sources = kFlushChunk/2 pair records) against R targets.
+// MASK: the chunk may contain one of this CTA's own targets; its mass is zeroed for that
+// target so the potential carries no self term (the force self term is exactly 0 anyway).
+template <int R, bool PACKED, bool POT, bool MASK>
+__device__ __forceinline__ void chunk_interact(Target<PACKED, POT> (&t)[R], const float4* __restrict__ rec,
+                                               float eps2, long long j_first, const long long (&ti)[R]) {
+    if constexpr (PACKED) {
+        const f2 e2 = f2_make(eps2, eps2);
+#pragma unroll
+        for (int u = 0; u < kFlushChunk / 2; ++u) {
+            const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(rec + 2 * u);
+            const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(rec + 2 * u + 1);
+            f2 xj{A.x}, yj{A.y}, zj{B.x}, mj{B.y};
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                f2 m = mj;
+                if (MASK) {
+                    float m0, m1;
+                    f2_split(mj, m0, m1);
+                    const long long j0 = j_first + 2 * u;
+                    m = f2_make(j0 == ti[r] ? 0.f : m0, j0 + 1 == ti[r] ? 0.f : m1);
+                }
+                t[r].interact(xj, yj, zj, m, e2);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < kFlushChunk / 2; ++u) {
+            const float4 A = rec[2 * u];
+            const float4 B = rec[2 * u + 1];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                float m0 = B.z, m1 = B.w;
+                if (MASK) {
+                    const long long j0 = j_first + 2 * u;
+                    if (j0 == ti[r]) m0 = 0.f;
+                    if (j0 + 1 == ti[r]) m1 = 0.f;
+                }
+                t[r].interact(A, B, m0, m1, eps2);
+            }
+        }
+    }
+}
+
+}  // namespace nb

@@ -1,0 +1,1037 @@
+// nbody_b200.cu — C-ABI implementation (include/nbody_b200.h) over the sm_100a kernels.
+// Host-side mirror of the reference's frame schedule, src/systems/Physics.hpp:32-64:
+// which force evaluations a frame needs, the substep plan, and when cached device state
+// (accelerations, the FP32 j-stream) is still valid. No CPU fallback exists in this file.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+
+#include "ctx.cuh"
+#include "diag.cuh"
+#include "exact.cuh"
+#include "force_kernel.cuh"
+#include "state.cuh"
+
+using namespace nb;
+
+// ---------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+static int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define NB_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(NB_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_) + " (" +  \
+                                         __FILE__ + ":" + std::to_string(__LINE__) + ")");        \
+    } while (0)
+
+#define NB_TRY(expr)             \
+    do {                         \
+        int r_ = (expr);         \
+        if (r_ != NB_OK) return r_; \
+    } while (0)
+
+extern "C" const char* nb_last_error(void) { return g_last_error.c_str(); }
+extern "C" int nb_abi_version(void) { return NB_ABI_VERSION; }
+
+// ---------------------------------------------------------------------------------------
+// NCCL, resolved at run time
+// ---------------------------------------------------------------------------------------
+namespace {
+
+struct NcclId {
+    char bytes[128];
+};
+typedef int (*fn_GetUniqueId)(NcclId*);
+typedef int (*fn_CommInitRank)(void**, int, NcclId, int);
+typedef int (*fn_CommDestroy)(void*);
+typedef int (*fn_AllGather)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*fn_AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_Group)(void);
+typedef const char* (*fn_ErrStr)(int);
+
+struct Nccl {
+    void* handle = nullptr;
+    fn_GetUniqueId GetUniqueId = nullptr;
+    fn_CommInitRank CommInitRank = nullptr;
+    fn_CommDestroy CommDestroy = nullptr;
+    fn_AllGather AllGather = nullptr;
+    fn_AllReduce AllReduce = nullptr;
+    fn_Group GroupStart = nullptr, GroupEnd = nullptr;
+    fn_ErrStr GetErrorString = nullptr;
+};
+Nccl g_nccl;
+
+// ncclDataType_t / ncclRedOp_t values (stable across NCCL 2.x)
+constexpr int kNcclFloat32 = 7, kNcclFloat64 = 8, kNcclUint32 = 3, kNcclSum = 0, kNcclMax = 2;
+
+int load_nccl() {
+    if (g_nccl.handle) return NB_OK;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);  // torch's copy if already mapped
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(NB_ERR_NCCL, std::string("cannot load libnccl.so.2: ") + dlerror());
+    g_nccl.GetUniqueId = (fn_GetUniqueId)dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (fn_CommInitRank)dlsym(h, "ncclCommInitRank");
+    g_nccl.CommDestroy = (fn_CommDestroy)dlsym(h, "ncclCommDestroy");
+    g_nccl.AllGather = (fn_AllGather)dlsym(h, "ncclAllGather");
+    g_nccl.AllReduce = (fn_AllReduce)dlsym(h, "ncclAllReduce");
+    g_nccl.GroupStart = (fn_Group)dlsym(h, "ncclGroupStart");
+    g_nccl.GroupEnd = (fn_Group)dlsym(h, "ncclGroupEnd");
+    g_nccl.GetErrorString = (fn_ErrStr)dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce || !g_nccl.GroupStart ||
+        !g_nccl.GroupEnd)
+        return fail(NB_ERR_NCCL, "libnccl.so.2 lacks a required symbol");
+    g_nccl.handle = h;
+    return NB_OK;
+}
+
+int nccl_fail(int rc, const char* what) {
+    return fail(NB_ERR_NCCL,
+                std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"));
+}
+#define NB_NCCL(expr)                            \
+    do {                                         \
+        int rc_ = (expr);                        \
+        if (rc_ != 0) return nccl_fail(rc_, #expr); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------
+// force-kernel table and launch planning
+// ---------------------------------------------------------------------------------------
+constexpr int kNT = 128;
+typedef void (*ForceFn)(const StepParams);
+
+struct KernelEntry {
+    int r, packed, pot;
+    ForceFn fn;
+};
+
+const KernelEntry kKernels[] = {
+    {4, 1, 0, force_kernel<kNT, 4, true, false, 4>},  {2, 1, 0, force_kernel<kNT, 2, true, false, 4>},
+    {1, 1, 0, force_kernel<kNT, 1, true, false, 4>},  {4, 0, 0, force_kernel<kNT, 4, false, false, 4>},
+    {2, 0, 0, force_kernel<kNT, 2, false, false, 4>}, {1, 0, 0, force_kernel<kNT, 1, false, false, 4>},
+    {2, 1, 1, force_kernel<kNT, 2, true, true, 4>},   {1, 1, 1, force_kernel<kNT, 1, true, true, 4>},
+    {2, 0, 1, force_kernel<kNT, 2, false, true, 4>},  {1, 0, 1, force_kernel<kNT, 1, false, true, 4>},
+};
+constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
+
+const KernelEntry* find_kernel(int r, int packed, int pot) {
+    for (int k = 0; k < kNumKernels; ++k)
+        if (kKernels[k].r == r && kKernels[k].packed == packed && kKernels[k].pot == pot) return &kKernels[k];
+    return nullptr;
+}
+
+// Choose targets-per-thread and the source split so the grid fills whole waves of SMs.
+LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles, bool pot) {
+    LaunchPlan best;
+    double best_score = -1.0;
+    const int packed = c->forced_packed >= 0 ? c->forced_packed : 1;
+    const int r_opts_force[] = {4, 2, 1};
+    const int r_opts_pot[] = {2, 1};
+    const int* r_opts = pot ? r_opts_pot : r_opts_force;
+    const int n_opts = pot ? 2 : 3;
+    for (int q = 0; q < n_opts; ++q) {
+        const int r = r_opts[q];
+        if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 2 && r == 2)) continue;
+        const KernelEntry* ke = find_kernel(r, packed, pot ? 1 : 0);
+        if (!ke) continue;
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 1;
+        const long long slots = (long long)c->sm_count * per_sm;
+        const long long n_it = std::max<long long>(1, (n_targets + (long long)kNT * r - 1) / ((long long)kNT * r));
+        const int seg_hi = (int)std::min<long long>(kMaxSegments, std::max<long long>(1, n_src_tiles));
+        for (int nseg = 1; nseg <= seg_hi; ++nseg) {
+            if (c->forced_nseg && nseg != c->forced_nseg && !(c->forced_nseg > seg_hi && nseg == seg_hi)) continue;
+            const long long units = n_it * nseg;
+            const long long waves = (units + slots - 1) / slots;
+            double eff = (double)units / (double)(waves * slots);
+            // larger R amortises shared-memory reads; each extra segment costs a partial round-trip
+            const double score = eff * (r == 4 ? 1.0 : (r == 2 ? 0.97 : 0.90)) * (1.0 - 0.002 * (nseg - 1));
+            if (score > best_score) {
+                best_score = score;
+                best.variant = (int)(ke - kKernels);
+                best.r = r;
+                best.nseg = nseg;
+                best.n_itiles = n_it;
+                best.ctas_per_sm = per_sm;
+            }
+        }
+    }
+    return best;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// AoS (reference component layout) <-> SoA device state
+// ---------------------------------------------------------------------------------------
+namespace {
+
+// staging: [pos dim*n doubles][vel dim*n doubles]; rows [0,n) of the SoA state
+__global__ void __launch_bounds__(256) unpack_aos_kernel(const double* pos, const double* vel, int dim, long long n,
+                                                         StateView s) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        s.x[k][i] = k < dim ? pos[i * dim + k] : 0.0;
+        s.v[k][i] = k < dim ? vel[i * dim + k] : 0.0;
+        s.a[k][i] = 0.0;   // fresh entities start with Acceleration{0}, Physics.hpp:97
+        s.a0[k][i] = 0.0;  // and PrevAcceleration{0}, :98
+    }
+}
+
+// which: 0 x, 1 v, 2 a -> out[(i - lo) * dim + k] for rows [lo,hi)
+__global__ void __launch_bounds__(256) pack_aos_kernel(StateView s, int which, int dim, double* out) {
+    const long long i = s.lo + blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= s.hi) return;
+    double* const* src = which == 0 ? s.x : (which == 1 ? s.v : s.a);
+    for (int k = 0; k < dim; ++k) out[(i - s.lo) * dim + k] = src[k][i];
+}
+
+inline unsigned int blocks_for(long long n, int threads) { return (unsigned int)std::max<long long>(1, (n + threads - 1) / threads); }
+
+void free_bodies(nb_ctx* c) {
+    cudaFree(c->state); cudaFree(c->mass); cudaFree(c->pinned); cudaFree(c->live);
+    cudaFree(c->pk[0]); cudaFree(c->pk[1]); cudaFree(c->part); cudaFree(c->tile_counter);
+    cudaFree(c->diag_part); cudaFree(c->dpk); cudaFree(c->staging);
+    c->state = nullptr; c->mass = nullptr; c->pinned = c->live = nullptr; c->pk[0] = c->pk[1] = nullptr;
+    c->part = nullptr; c->tile_counter = nullptr; c->diag_part = nullptr; c->dpk = nullptr; c->staging = nullptr;
+    c->cap = 0; c->staging_bytes = 0; c->part_slots = 0; c->i_cap = 0; c->counter_cap = 0; c->diag_part_rows = 0;
+}
+
+int ensure_staging(nb_ctx* c, size_t bytes) {
+    if (bytes <= c->staging_bytes) return NB_OK;
+    if (c->staging) cudaFree(c->staging);
+    c->staging = nullptr;
+    c->staging_bytes = 0;
+    NB_CUDA(cudaMalloc(&c->staging, bytes));
+    c->staging_bytes = bytes;
+    return NB_OK;
+}
+
+// (Re)size every per-body buffer for n bodies and derive the rank's target range and plans.
+int size_for(nb_ctx* c, long long n) {
+    const long long tiles = std::max<long long>(1, (n + kTileBodies - 1) / kTileBodies);
+    c->tiles_per_rank = (tiles + c->world - 1) / c->world;
+    c->n_tiles = c->tiles_per_rank * c->world;
+    c->lo = std::min<long long>(n, (long long)c->rank * c->tiles_per_rank * kTileBodies);
+    c->hi = std::min<long long>(n, (long long)(c->rank + 1) * c->tiles_per_rank * kTileBodies);
+    c->n = n;
+    const long long rows = c->n_tiles * kTileBodies;
+    if (rows > c->cap) {
+        free_bodies(c);
+        NB_CUDA(cudaMalloc(&c->state, sizeof(double) * 12 * rows));
+        NB_CUDA(cudaMalloc(&c->mass, sizeof(float) * rows));
+        NB_CUDA(cudaMalloc(&c->pinned, rows));
+        NB_CUDA(cudaMalloc(&c->live, rows));
+        NB_CUDA(cudaMalloc(&c->pk[0], sizeof(float) * 4 * rows));
+        NB_CUDA(cudaMalloc(&c->pk[1], sizeof(float) * 4 * rows));
+        NB_CUDA(cudaMalloc(&c->dpk, sizeof(float4) * rows));
+        c->cap = rows;
+    }
+    NB_CUDA(cudaMemsetAsync(c->state, 0, sizeof(double) * 12 * c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->mass, 0, sizeof(float) * c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->pinned, 0, c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->live, 0, c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->pk[0], 0, sizeof(float) * 4 * c->cap, c->stream));  // padding rows stay m = 0
+    NB_CUDA(cudaMemsetAsync(c->pk[1], 0, sizeof(float) * 4 * c->cap, c->stream));
+
+    // launch plans: all sources in one launch, or (sharded) own sources first, the rest after the exchange
+    const long long n_local = c->hi - c->lo;
+    int slots = 1;
+    for (int pot = 0; pot < 2; ++pot) {
+        c->plans[0][pot] = make_plan(c, n_local, c->n_tiles, pot != 0);
+        c->plans[1][pot] = make_plan(c, n_local, c->tiles_per_rank, pot != 0);
+        c->plans[2][pot] = make_plan(c, n_local, std::max<long long>(1, c->n_tiles - c->tiles_per_rank), pot != 0);
+        for (int w = 0; w < 3; ++w) slots = std::max(slots, c->plans[w][pot].nseg);
+    }
+    const long long i_cap = ((std::max<long long>(n_local, 1) + 1023) / 1024) * 1024;
+    if (slots > c->part_slots || i_cap > c->i_cap) {
+        cudaFree(c->part);
+        c->part = nullptr;
+        NB_CUDA(cudaMalloc(&c->part, sizeof(double) * (size_t)(1 + slots) * 4 * i_cap));
+        c->part_slots = slots;
+        c->i_cap = i_cap;
+    }
+    const long long max_itiles = (std::max<long long>(n_local, 1) + kNT - 1) / kNT;  // R = 1 upper bound
+    if (max_itiles > c->counter_cap) {
+        cudaFree(c->tile_counter);
+        cudaFree(c->diag_part);
+        c->tile_counter = nullptr;
+        c->diag_part = nullptr;
+        NB_CUDA(cudaMalloc(&c->tile_counter, sizeof(unsigned int) * max_itiles));
+        const long long rows_d = std::max<long long>(max_itiles, blocks_for(n_local, kDiagThreads));
+        NB_CUDA(cudaMalloc(&c->diag_part, sizeof(double) * kDiagValues * rows_d));
+        c->counter_cap = max_itiles;
+        c->diag_part_rows = rows_d;
+    }
+    NB_CUDA(cudaMemsetAsync(c->tile_counter, 0, sizeof(unsigned int) * c->counter_cap, c->stream));
+    return NB_OK;
+}
+
+int mass_exponent(const float* mass, long long n) {
+    float mx = 0.f;
+    for (long long i = 0; i < n; ++i)
+        if (mass[i] > mx && mass[i] <= 3.4028234663852886e38f) mx = mass[i];
+    if (!(mx > 0.f)) return 0;
+    int e;
+    frexpf(mx, &e);  // mx = f * 2^e, f in [0.5, 1): packed masses land in (0, 1)
+    return e;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// lifetime and configuration
+// ---------------------------------------------------------------------------------------
+extern "C" int nb_default_config(nb_config* out) {
+    if (!out) return fail(NB_ERR_INVALID, "nb_default_config: null");
+    out->g = 6.67430e-11;            // Constants.hpp:87
+    out->softening = 4.0f;           // :89
+    out->max_speed = 0.0f;           // :90
+    out->integrator = NB_INTEGRATOR_VERLET;  // Config.hpp:25
+    out->max_substep = 1.0e9f;       // Constants.hpp:99
+    out->max_substeps_per_frame = 200;  // :100
+    return NB_OK;
+}
+
+static int create_common(int device, int rank, int world, nb_ctx** out) {
+    if (!out) return fail(NB_ERR_INVALID, "nb_create: null out pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0)
+        return fail(NB_ERR_NO_DEVICE, std::string("no CUDA device (this library has no CPU path): ") +
+                                          (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0"));
+    if (device < 0 || device >= count) return fail(NB_ERR_INVALID, "nb_create: device index out of range");
+    NB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    NB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(NB_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
+    nb_ctx* c = new nb_ctx();
+    c->device = device;
+    c->rank = rank;
+    c->world = world;
+    c->sm_count = prop.multiProcessorCount;
+    nb_default_config(&c->cfg);
+    int lo_prio = 0, hi_prio = 0;
+    cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+    NB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    NB_CUDA(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, hi_prio));
+    NB_CUDA(cudaEventCreate(&c->ev_timer0));
+    NB_CUDA(cudaEventCreate(&c->ev_timer1));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
+    NB_CUDA(cudaMalloc(&c->extent, sizeof(unsigned int) * (kExtentSlots + 4)));
+    NB_CUDA(cudaMemset(c->extent, 0, sizeof(unsigned int) * (kExtentSlots + 4)));
+    NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * 64));
+    NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * 64 * 16));
+    if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
+    if (const char* v = getenv("NB_FORCE_PACKED")) c->forced_packed = atoi(v);
+    if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
+    *out = c;
+    return NB_OK;
+}
+
+extern "C" int nb_create(int device, nb_ctx** out) { return create_common(device, 0, 1, out); }
+
+extern "C" int nb_comm_unique_id(void* out_id_128) {
+    if (!out_id_128) return fail(NB_ERR_INVALID, "nb_comm_unique_id: null");
+    NB_TRY(load_nccl());
+    NcclId id;
+    NB_NCCL(g_nccl.GetUniqueId(&id));
+    memcpy(out_id_128, id.bytes, 128);
+    return NB_OK;
+}
+
+extern "C" int nb_create_sharded(int device, int rank, int world, const void* nccl_unique_id, nb_ctx** out) {
+    if (world < 1 || rank < 0 || rank >= world) return fail(NB_ERR_INVALID, "nb_create_sharded: bad rank/world");
+    if (world > 1 && !nccl_unique_id) return fail(NB_ERR_INVALID, "nb_create_sharded: null id");
+    NB_TRY(create_common(device, rank, world, out));
+    if (world > 1) {
+        NB_TRY(load_nccl());
+        NcclId id;
+        memcpy(id.bytes, nccl_unique_id, 128);
+        NB_NCCL(g_nccl.CommInitRank(&(*out)->nccl_comm, world, id, rank));
+    }
+    return NB_OK;
+}
+
+extern "C" void nb_destroy(nb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->comm_stream);
+    if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+    free_bodies(c);
+    cudaFree(c->extent);
+    cudaFree(c->totals);
+    cudaFreeHost(c->h_totals);
+    for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
+    cudaEventDestroy(c->ev_timer0);
+    cudaEventDestroy(c->ev_timer1);
+    cudaEventDestroy(c->ev_packed);
+    cudaEventDestroy(c->ev_gathered);
+    cudaStreamDestroy(c->stream);
+    cudaStreamDestroy(c->comm_stream);
+    delete c;
+}
+
+extern "C" int nb_set_config(nb_ctx* c, const nb_config* cfg) {
+    if (!c || !cfg) return fail(NB_ERR_INVALID, "nb_set_config: null");
+    if (cfg->integrator != NB_INTEGRATOR_EULER && cfg->integrator != NB_INTEGRATOR_VERLET)
+        return fail(NB_ERR_INVALID, "nb_set_config: integrator must be 0 (Euler) or 1 (Verlet)");
+    const bool repack = cfg->softening != c->cfg.softening || cfg->g != c->cfg.g;
+    c->cfg = *cfg;
+    if (repack) c->acc_valid = false;  // accelerations depend on G and epsilon
+    return NB_OK;
+}
+
+extern "C" int nb_get_config(nb_ctx* c, nb_config* out) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_get_config: null");
+    *out = c->cfg;
+    return NB_OK;
+}
+
+extern "C" int64_t nb_num_bodies(nb_ctx* c) { return c ? c->n : -1; }
+
+extern "C" int nb_local_range(nb_ctx* c, int64_t* lo, int64_t* hi) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_local_range: null");
+    if (lo) *lo = c->lo;
+    if (hi) *hi = c->hi;
+    return NB_OK;
+}
+
+extern "C" int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub) {
+    // Physics.hpp:268-271, float arithmetic throughout
+    const float cap = std::max(1e-6f, max_substep);
+    int n_steps = static_cast<int>(std::ceil(dt / cap));
+    n_steps = std::max(1, std::min(n_steps, std::max(1, (int)max_substeps_per_frame)));
+    if (dt_sub) *dt_sub = dt / static_cast<float>(n_steps);
+    return n_steps;
+}
+
+// ---------------------------------------------------------------------------------------
+// exchange between ranks (target-partitioned contexts)
+// ---------------------------------------------------------------------------------------
+namespace {
+
+// All-gather generation `gen`'s j-stream slices in place and max-reduce the rotating extent
+// slots, on the comm stream, after everything enqueued so far on the main stream.
+int exchange_packed(nb_ctx* c, int gen, bool main_waits) {
+    if (c->world <= 1) return NB_OK;
+    NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
+    NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
+    float* buf = c->pk[gen & 1];
+    const size_t count = (size_t)c->tiles_per_rank * kTileBodies * 4;  // floats per rank
+    NB_NCCL(g_nccl.GroupStart());
+    NB_NCCL(g_nccl.AllGather(buf + (size_t)c->rank * count, buf, count, kNcclFloat32, c->nccl_comm, c->comm_stream));
+    // only the slot this generation's epilogue wrote: the others are being read by kernels in flight
+    unsigned int* slot = c->extent + (gen % kExtentSlots);
+    NB_NCCL(g_nccl.AllReduce(slot, slot, 1, kNcclUint32, kNcclMax, c->nccl_comm, c->comm_stream));
+    NB_NCCL(g_nccl.GroupEnd());
+    NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
+    if (main_waits) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+    return NB_OK;
+}
+
+// Measure the extent of the current positions, open a new generation and pack it.
+int prepare_packed(nb_ctx* c) {
+    const StateView s = c->view();
+    c->gen += 1;
+    const int g = c->gen;
+    NB_CUDA(cudaMemsetAsync(c->extent, 0, sizeof(unsigned int) * kExtentSlots, c->stream));
+    const long long n_local = c->hi - c->lo;
+    const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kStateThreads), 4 * c->sm_count);
+    extent_kernel<<<grid, kStateThreads, 0, c->stream>>>(s, c->extent, (g + kExtentSlots - 1) % kExtentSlots,
+                                                         g % kExtentSlots);
+    c->kernel_launches++;
+    if (c->world > 1) {
+        // the pack below needs the GLOBAL extent: reduce it first (blocking the main stream)
+        NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
+        NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
+        NB_NCCL(g_nccl.AllReduce(c->extent, c->extent, kExtentSlots, kNcclUint32, kNcclMax, c->nccl_comm,
+                                 c->comm_stream));
+        NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+    }
+    if (n_local > 0) {
+        pack_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(
+            s, c->pk[g & 1], c->extent, g, c->mass_exp, c->cfg.g, c->cfg.softening);
+        c->kernel_launches++;
+    }
+    NB_CUDA(cudaGetLastError());
+    NB_TRY(exchange_packed(c, g, true));
+    c->packed_valid = true;
+    return NB_OK;
+}
+
+int prof_begin(nb_ctx* c) {
+    if (!c->profile) return NB_OK;
+    if (c->prof_used + 2 > c->prof_events.size()) {
+        for (int k = 0; k < 2; ++k) {
+            cudaEvent_t e;
+            NB_CUDA(cudaEventCreate(&e));
+            c->prof_events.push_back(e);
+        }
+    }
+    NB_CUDA(cudaEventRecord(c->prof_events[c->prof_used], c->stream));
+    return NB_OK;
+}
+int prof_end(nb_ctx* c) {
+    if (!c->profile) return NB_OK;
+    NB_CUDA(cudaEventRecord(c->prof_events[c->prof_used + 1], c->stream));
+    c->prof_used += 2;
+    return NB_OK;
+}
+
+// One launch of the force kernel. which: 0 all sources, 1 own sources (partial only),
+// 2 remote sources (+ partial from launch 1, + epilogue).
+int launch_force(nb_ctx* c, int which, int mode, bool pot, double dt) {
+    const long long n_local = c->hi - c->lo;
+    if (n_local <= 0) return NB_OK;
+    const LaunchPlan& pl = c->plans[which][pot ? 1 : 0];
+    const KernelEntry& ke = kKernels[pl.variant];
+    StepParams p;
+    const StateView s = c->view();
+    for (int k = 0; k < 3; ++k) {
+        p.x[k] = s.x[k]; p.v[k] = s.v[k]; p.a[k] = s.a[k]; p.a0[k] = s.a0[k];
+    }
+    p.mass = c->mass; p.pinned = c->pinned; p.live = c->live;
+    p.pk_cur = c->pk[c->gen & 1];
+    p.pk_next = c->pk[(c->gen + 1) & 1];
+    p.extent = c->extent;
+    p.part = c->part;
+    p.tile_counter = c->tile_counter;
+    p.diag_part = c->diag_part;
+    p.n = c->n;
+    p.n_tiles = c->n_tiles;
+    p.i_lo = c->lo; p.i_hi = c->hi;
+    p.i_cap = c->i_cap;
+    const long long own_lo = (long long)c->rank * c->tiles_per_rank;
+    p.hole_lo = c->n_tiles; p.hole_len = 0;
+    if (which == 0) { p.j_tile_lo = 0; p.j_tile_hi = c->n_tiles; }
+    else if (which == 1) { p.j_tile_lo = own_lo; p.j_tile_hi = own_lo + c->tiles_per_rank; }
+    else { p.j_tile_lo = 0; p.j_tile_hi = c->n_tiles - c->tiles_per_rank; p.hole_lo = own_lo; p.hole_len = c->tiles_per_rank; }
+    p.nseg = pl.nseg;
+    p.gen = c->gen;
+    p.mode = which == 1 ? (int)kPartialOnly : mode;
+    p.accumulate = which == 2 ? 1 : 0;
+    p.mass_exp = c->mass_exp;
+    p.softening = c->cfg.softening;
+    p.max_speed = c->cfg.max_speed;
+    p.g = c->cfg.g;
+    p.dt = dt;
+    p.half_dt2 = 0.5 * dt * dt;  // Physics.hpp:300
+    const long long n_it = (n_local + (long long)kNT * pl.r - 1) / ((long long)kNT * pl.r);
+    NB_TRY(prof_begin(c));
+    ke.fn<<<(unsigned int)(n_it * pl.nseg), kNT, 0, c->stream>>>(p);
+    NB_CUDA(cudaGetLastError());
+    NB_TRY(prof_end(c));
+    c->kernel_launches++;
+    c->interactions += (double)n_local * (double)(p.j_tile_hi - p.j_tile_lo) * kTileBodies;
+    if (which != 1 && pot) {
+        c->step_diag_rows = n_it;
+        c->step_diag_valid = true;
+    }
+    return NB_OK;
+}
+
+// One force evaluation over all sources with epilogue `mode`; advances the generation when
+// the epilogue packed the next j-stream.
+int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
+    if (!c->packed_valid) NB_TRY(prepare_packed(c));
+    const bool packs = (mode == kEuler || mode == kVerletKickDrift);
+    if (c->world > 1 && c->plans[2][0].n_itiles > 0 && c->n_tiles > c->tiles_per_rank) {
+        // own sources need no communication: start on them while the exchange of the
+        // previous epilogue's pack is still in flight, then finish with the remote ones
+        NB_TRY(launch_force(c, 1, mode, pot, dt));
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+        NB_TRY(launch_force(c, 2, mode, pot, dt));
+    } else {
+        NB_TRY(launch_force(c, 0, mode, pot, dt));
+    }
+    c->force_evals++;
+    if (packs) {
+        c->gen += 1;
+        NB_TRY(exchange_packed(c, c->gen, false));  // consumed by the next pass after its own-sources launch
+    }
+    return NB_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
+// state upload / download
+// ---------------------------------------------------------------------------------------
+static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel, const float* mass,
+                      const uint8_t* pinned, int dim) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_upload: null context");
+    if (n < 0 || (n > 0 && (!pos || !vel || !mass))) return fail(NB_ERR_INVALID, "nb_upload: null array");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_TRY(size_for(c, n));
+    c->dim = dim;
+    c->mass_exp = mass_exponent(mass, n);
+    c->acc_valid = false;
+    c->packed_valid = false;
+    c->step_diag_valid = false;
+    if (n == 0) return NB_OK;
+    const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n;
+    NB_TRY(ensure_staging(c, 2 * vec_bytes));
+    double* d_pos = static_cast<double*>(c->staging);
+    double* d_vel = d_pos + (size_t)dim * n;
+    NB_CUDA(cudaMemcpyAsync(d_pos, pos, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(d_vel, vel, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(c->mass, mass, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
+    if (pinned) NB_CUDA(cudaMemcpyAsync(c->pinned, pinned, (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    unpack_aos_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_pos, d_vel, dim, n, c->view());
+    NB_CUDA(cudaGetLastError());
+    c->kernel_launches++;
+    NB_TRY(prepare_packed(c));
+    // the borrowed host arrays may be pageable: do not return while a copy could still read them
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+extern "C" int nb_upload(nb_ctx* c, int64_t n, const double* pos_xy, const double* vel_xy, const float* mass,
+                         const uint8_t* pinned) {
+    return upload_dim(c, n, pos_xy, vel_xy, mass, pinned, 2);
+}
+extern "C" int nb_upload3(nb_ctx* c, int64_t n, const double* pos_xyz, const double* vel_xyz, const float* mass,
+                          const uint8_t* pinned) {
+    return upload_dim(c, n, pos_xyz, vel_xyz, mass, pinned, 3);
+}
+
+static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int dim) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_download: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    const long long n_local = c->hi - c->lo;
+    if (n_local <= 0) return NB_OK;
+    const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n_local;
+    NB_TRY(ensure_staging(c, 3 * vec_bytes));
+    double* out[3] = {pos, vel, acc};
+    const StateView s = c->view();
+    for (int w = 0; w < 3; ++w) {
+        if (!out[w]) continue;
+        double* d = static_cast<double*>(c->staging) + (size_t)w * dim * n_local;
+        pack_aos_kernel<<<blocks_for(n_local, 256), 256, 0, c->stream>>>(s, w, dim, d);
+        c->kernel_launches++;
+        NB_CUDA(cudaMemcpyAsync(out[w] + (size_t)c->lo * dim, d, vec_bytes, cudaMemcpyDeviceToHost, c->stream));
+    }
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+extern "C" int nb_download(nb_ctx* c, double* pos_xy, double* vel_xy, double* acc_xy) {
+    return download_dim(c, pos_xy, vel_xy, acc_xy, 2);
+}
+extern "C" int nb_download3(nb_ctx* c, double* pos_xyz, double* vel_xyz, double* acc_xyz) {
+    return download_dim(c, pos_xyz, vel_xyz, acc_xyz, 3);
+}
+
+// ---------------------------------------------------------------------------------------
+// FP64 exact path (exact.cuh): unfused, every kernel reads state written by the previous one
+// ---------------------------------------------------------------------------------------
+static bool use_exact(const nb_ctx* c) {
+    if (c->world > 1) return false;
+    if (c->precision == NB_PRECISION_FP64_EXACT) return true;
+    return c->precision == NB_PRECISION_AUTO && c->n <= NB_EXACT_AUTO_MAX;
+}
+
+extern "C" int nb_set_precision(nb_ctx* c, int precision) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_set_precision: null context");
+    if (precision < NB_PRECISION_AUTO || precision > NB_PRECISION_FP64_EXACT)
+        return fail(NB_ERR_INVALID, "nb_set_precision: unknown mode");
+    if (precision == NB_PRECISION_FP64_EXACT && c->world > 1)
+        return fail(NB_ERR_INVALID, "nb_set_precision: FP64_EXACT needs a single-GPU context");
+    if (precision != c->precision) c->acc_valid = false;
+    c->precision = precision;
+    return NB_OK;
+}
+
+static int exact_force(nb_ctx* c) {
+    exact_force_kernel<<<blocks_for(c->n, kExactThreads), kExactThreads, 0, c->stream>>>(c->view(), c->cfg.g,
+                                                                                        c->cfg.softening);
+    NB_CUDA(cudaGetLastError());
+    c->kernel_launches++;
+    c->force_evals++;
+    c->interactions += (double)c->n * (double)c->n;
+    return NB_OK;
+}
+
+static int exact_verlet(nb_ctx* c, double h, long long n_sub) {
+    const unsigned int grid = blocks_for(c->n, kStateThreads);
+    for (long long k = 0; k < n_sub; ++k) {
+        verlet_drift_kernel<<<grid, kStateThreads, 0, c->stream>>>(c->view(), h, 0.5 * h * h);
+        NB_TRY(exact_force(c));
+        verlet_kick_kernel<<<grid, kStateThreads, 0, c->stream>>>(c->view(), h, c->cfg.max_speed);
+        c->kernel_launches += 2;
+    }
+    NB_CUDA(cudaGetLastError());
+    c->packed_valid = false;
+    return NB_OK;
+}
+
+static int exact_euler_move(nb_ctx* c, double h) {
+    euler_move_kernel<<<blocks_for(c->n, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h, c->cfg.max_speed);
+    NB_CUDA(cudaGetLastError());
+    c->kernel_launches++;
+    c->packed_valid = false;
+    return NB_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// the hot path: compute_gravity / integrate / fused frames
+// ---------------------------------------------------------------------------------------
+extern "C" int nb_compute_gravity(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_compute_gravity: null context");
+    if (c->n == 0) return NB_OK;  // Physics.hpp:208
+    NB_CUDA(cudaSetDevice(c->device));
+    if (use_exact(c)) NB_TRY(exact_force(c));
+    else NB_TRY(force_pass(c, kForceOnly, false, 0.0));
+    c->acc_valid = true;
+    return NB_OK;
+}
+
+// n_sub velocity Verlet substeps (Physics.hpp:296-325) starting from Acceleration == a(x).
+static int verlet_substeps(nb_ctx* c, double h, long long n_sub, bool more_follow, bool pot) {
+    if (n_sub <= 0) return NB_OK;
+    const long long n_local = c->hi - c->lo;
+    // the first drift of a call cannot ride in an epilogue: stand-alone kernel, new generation
+    if (n_local > 0) {
+        verlet_drift_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
+                                                                                               0.5 * h * h);
+        c->kernel_launches++;
+    }
+    c->packed_valid = false;
+    for (long long k = 0; k < n_sub; ++k) {
+        const bool last = (k + 1 == n_sub) && !more_follow;
+        NB_TRY(force_pass(c, last ? kVerletKick : kVerletKickDrift, pot && (k + 1 == n_sub), h));
+    }
+    return NB_OK;
+}
+
+extern "C" int nb_integrate(nb_ctx* c, float dt) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_integrate: null context");
+    if (c->n == 0) return NB_OK;
+    NB_CUDA(cudaSetDevice(c->device));
+    float dt_sub;
+    const int n_steps = nb_substep_plan(dt, c->cfg.max_substep, c->cfg.max_substeps_per_frame, &dt_sub);
+    const double h = (double)dt_sub;
+    const long long n_local = c->hi - c->lo;
+    if (use_exact(c)) {
+        if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
+            for (int k = 0; k < n_steps; ++k) {
+                NB_TRY(exact_euler_move(c, h));
+                if (k + 1 < n_steps) NB_TRY(exact_force(c));  // Physics.hpp:292
+            }
+            c->acc_valid = false;
+        } else {
+            NB_TRY(exact_verlet(c, h, n_steps));
+            c->acc_valid = true;
+        }
+        return NB_OK;
+    }
+    if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
+        // kick/drift with the stored acceleration, then (gravity, kick/drift) per further substep
+        if (n_local > 0) {
+            euler_move_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
+                                                                                                 c->cfg.max_speed);
+            c->kernel_launches++;
+        }
+        c->packed_valid = false;
+        c->acc_valid = false;
+        for (int k = 1; k < n_steps; ++k) NB_TRY(force_pass(c, kEuler, false, h));
+    } else {
+        NB_TRY(verlet_substeps(c, h, n_steps, false, false));
+        c->acc_valid = true;  // Physics.hpp:324
+    }
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_step: null context");
+    if (n_frames < 0) return fail(NB_ERR_INVALID, "nb_step: negative frame count");
+    if (c->n == 0 || n_frames == 0) return NB_OK;
+    NB_CUDA(cudaSetDevice(c->device));
+    float dt_sub;
+    const int n_steps = nb_substep_plan(dt_eff, c->cfg.max_substep, c->cfg.max_substeps_per_frame, &dt_sub);
+    const double h = (double)dt_sub;
+    const long long total = n_frames * (long long)n_steps;
+    c->step_diag_exact = false;
+    if (use_exact(c)) {
+        if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
+            for (long long k = 0; k < total; ++k) {
+                NB_TRY(exact_force(c));
+                NB_TRY(exact_euler_move(c, h));
+            }
+            c->acc_valid = false;
+        } else {
+            if (!c->acc_valid) NB_TRY(exact_force(c));
+            c->acc_valid = true;
+            NB_TRY(exact_verlet(c, h, total));
+        }
+        c->step_diag_exact = pot;
+        return NB_OK;
+    }
+    if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
+        // frame = gravity system + n_steps x (kick/drift [+ gravity]): n_steps fused passes
+        for (long long k = 0; k < total; ++k) NB_TRY(force_pass(c, kEuler, pot && (k + 1 == total), h));
+        c->acc_valid = false;  // Acceleration holds a(x) of the positions before the last move
+    } else {
+        // the gravity system's evaluation is only needed when Acceleration != a(x)
+        if (!c->acc_valid) NB_TRY(force_pass(c, kForceOnly, false, 0.0));
+        c->acc_valid = true;
+        NB_TRY(verlet_substeps(c, h, total, false, pot));
+    }
+    return NB_OK;
+}
+
+extern "C" int nb_step(nb_ctx* c, float dt_eff, int64_t n_frames) { return step_impl(c, dt_eff, n_frames, false); }
+extern "C" int nb_step_with_diagnostics(nb_ctx* c, float dt_eff, int64_t n_frames) {
+    return step_impl(c, dt_eff, n_frames, true);
+}
+
+// ---------------------------------------------------------------------------------------
+// diagnostics, zero_net_momentum, reset_scenario
+// ---------------------------------------------------------------------------------------
+namespace {
+
+// Sum `rows` per-CTA partial rows in fixed order on the device, combine the ranks' totals in
+// rank order on the host, and fill the reference's Diagnostics (Physics.hpp:163-176).
+int finish_diag(nb_ctx* c, long long rows, nb_diag* out) {
+    memset(out, 0, sizeof(*out));
+    double* h = c->h_totals;
+    for (int k = 0; k < kDiagValues; ++k) h[k] = 0.0;
+    if (rows > 0) {
+        sum_rows_kernel<<<1, 32, 0, c->stream>>>(c->diag_part, (int)rows, 10, kDiagValues, c->totals);
+        c->kernel_launches++;
+        NB_CUDA(cudaGetLastError());
+    } else {
+        NB_CUDA(cudaMemsetAsync(c->totals, 0, sizeof(double) * kDiagValues, c->stream));
+    }
+    double t[kDiagValues];
+    if (c->world > 1) {
+        // every rank receives every rank's totals and adds them in rank order: bit-identical everywhere
+        double* gathered = c->totals + 16;
+        NB_NCCL(g_nccl.AllGather(c->totals, gathered, kDiagValues, kNcclFloat64, c->nccl_comm, c->stream));
+        NB_CUDA(cudaMemcpyAsync(h, gathered, sizeof(double) * kDiagValues * c->world, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < kDiagValues; ++k) {
+            t[k] = 0.0;
+            for (int r = 0; r < c->world; ++r) t[k] += h[r * kDiagValues + k];
+        }
+    } else {
+        NB_CUDA(cudaMemcpyAsync(h, c->totals, sizeof(double) * kDiagValues, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < kDiagValues; ++k) t[k] = h[k];
+    }
+    const double M = t[8];
+    bool ok = t[9] == 0.0;
+    const double vals[10] = {t[0], t[1], t[0] + t[1], t[2], t[3], t[4],
+                             M > 0.0 ? t[5] / M : 0.0, M > 0.0 ? t[6] / M : 0.0, M > 0.0 ? t[7] / M : 0.0, M};
+    for (int k = 0; k < 10; ++k) ok = ok && std::isfinite(vals[k]);
+    if (!ok) {  // the reference returns a zeroed struct with ok = false (Physics.hpp:123,140-145)
+        out->ok = 0;
+        return NB_OK;
+    }
+    out->kinetic = vals[0];
+    out->potential = vals[1];
+    out->energy = vals[2];
+    for (int k = 0; k < 3; ++k) {
+        out->momentum[k] = vals[3 + k];
+        out->com[k] = vals[6 + k];
+    }
+    out->total_mass = M;
+    out->ok = 1;
+    return NB_OK;
+}
+
+}  // namespace
+
+extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_compute_diagnostics: null");
+    NB_CUDA(cudaSetDevice(c->device));
+    if (c->n == 0) {  // Physics.hpp:124-127
+        memset(out, 0, sizeof(*out));
+        out->ok = 1;
+        return NB_OK;
+    }
+    const StateView s = c->view();
+    const long long n_local = c->hi - c->lo;
+    NB_CUDA(cudaMemsetAsync(c->extent + kDiagExtentSlot, 0, sizeof(unsigned int), c->stream));
+    long long rows = 0;
+    if (n_local > 0) {
+        const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kDiagThreads), 4 * c->sm_count);
+        diag_extent_kernel<<<grid, kDiagThreads, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->lo, c->hi, c->extent);
+        c->kernel_launches++;
+    }
+    if (c->world > 1) {
+        unsigned int* slot = c->extent + kDiagExtentSlot;
+        NB_NCCL(g_nccl.AllReduce(slot, slot, 1, kNcclUint32, kNcclMax, c->nccl_comm, c->stream));
+    }
+    if (n_local > 0) {
+        diag_pack_kernel<<<blocks_for(n_local, kDiagThreads), kDiagThreads, 0, c->stream>>>(
+            s.x[0], s.x[1], s.x[2], c->mass, c->lo, c->hi, c->extent, c->mass_exp, c->dpk);
+        c->kernel_launches++;
+    }
+    if (c->world > 1) {
+        const size_t count = (size_t)c->tiles_per_rank * kTileBodies * 4;
+        float* buf = reinterpret_cast<float*>(c->dpk);
+        NB_NCCL(g_nccl.AllGather(buf + (size_t)c->rank * count, buf, count, kNcclFloat32, c->nccl_comm, c->stream));
+    }
+    if (n_local > 0) {
+        rows = blocks_for(n_local, kDiagThreads);
+        diag_potential_kernel<<<(unsigned int)rows, kDiagThreads, 0, c->stream>>>(
+            c->dpk, c->n, c->lo, c->hi, s.x[0], s.x[1], s.x[2], s.v[0], s.v[1], s.v[2], c->mass, c->extent, c->mass_exp,
+            c->cfg.g, c->cfg.softening, c->diag_part);
+        c->kernel_launches++;
+        c->interactions += (double)n_local * (double)c->n;
+    }
+    NB_CUDA(cudaGetLastError());
+    c->step_diag_valid = false;  // diag_part was overwritten
+    return finish_diag(c, rows, out);
+}
+
+extern "C" int nb_step_diagnostics(nb_ctx* c, nb_diag* out) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_step_diagnostics: null");
+    NB_CUDA(cudaSetDevice(c->device));
+    if (c->n == 0) {
+        memset(out, 0, sizeof(*out));
+        out->ok = 1;
+        return NB_OK;
+    }
+    if (c->step_diag_exact) return nb_compute_diagnostics(c, out);
+    if (!c->step_diag_valid && (c->hi - c->lo) > 0)
+        return fail(NB_ERR_INVALID, "nb_step_diagnostics: no nb_step_with_diagnostics since the last upload");
+    return finish_diag(c, (c->hi - c->lo) > 0 ? c->step_diag_rows : 0, out);
+}
+
+extern "C" int nb_zero_net_momentum(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_zero_net_momentum: null context");
+    if (c->n == 0) return NB_OK;
+    NB_CUDA(cudaSetDevice(c->device));
+    const StateView s = c->view();
+    const long long n_local = c->hi - c->lo;
+    const int grid = (int)std::min<long long>(blocks_for(n_local, kStateThreads), std::min<long long>(c->diag_part_rows, 2 * c->sm_count));
+    if (n_local > 0) {
+        momentum_partial_kernel<<<grid, kStateThreads, 0, c->stream>>>(s, c->diag_part);
+        sum_rows_kernel<<<1, 32, 0, c->stream>>>(c->diag_part, grid, 4, 4, c->totals);
+        c->kernel_launches += 2;
+    } else {
+        NB_CUDA(cudaMemsetAsync(c->totals, 0, sizeof(double) * 4, c->stream));
+    }
+    if (c->world > 1) {
+        // rank-ordered sum on the device would need another kernel; totals are 4 doubles, so
+        // gather them and let every rank add in rank order on the host
+        double* gathered = c->totals + 16;
+        NB_NCCL(g_nccl.AllGather(c->totals, gathered, 4, kNcclFloat64, c->nccl_comm, c->stream));
+        NB_CUDA(cudaMemcpyAsync(c->h_totals, gathered, sizeof(double) * 4 * c->world, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        double t[4] = {0, 0, 0, 0};
+        for (int r = 0; r < c->world; ++r)
+            for (int k = 0; k < 4; ++k) t[k] += c->h_totals[r * 4 + k];
+        NB_CUDA(cudaMemcpyAsync(c->totals, t, sizeof(double) * 4, cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    if (n_local > 0) {
+        momentum_apply_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(s, c->totals);
+        c->kernel_launches++;
+    }
+    NB_CUDA(cudaGetLastError());
+    c->step_diag_valid = false;
+    // velocities changed: the gather filter may change, positions did not -> the j-stream stays valid
+    return NB_OK;
+}
+
+extern "C" int nb_reset_scenario(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_reset_scenario: null context");
+    // Physics.hpp:87-115 with the constants of Constants.hpp:47-51; values pass through float
+    // (raylib::Vector2) before widening (Math.hpp:12)
+    const double central = 5.972e24, small = 7.342e22, radius = 3.844e8;
+    const float v = static_cast<float>(std::sqrt(c->cfg.g * central / radius));
+    const double pos[6] = {0.0, 0.0, (double)static_cast<float>(radius), 0.0, (double)static_cast<float>(-radius), 0.0};
+    const double vel[6] = {0.0, 0.0, 0.0, (double)v, 0.0, (double)-v};
+    const float mass[3] = {static_cast<float>(central), static_cast<float>(small), static_cast<float>(small)};
+    const uint8_t pinned[3] = {0, 0, 0};
+    NB_TRY(nb_upload(c, 3, pos, vel, mass, pinned));
+    return nb_zero_net_momentum(c);
+}
+
+// ---------------------------------------------------------------------------------------
+// synchronisation and measurement
+// ---------------------------------------------------------------------------------------
+extern "C" int nb_synchronize(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_synchronize: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    return NB_OK;
+}
+
+extern "C" int nb_timer_begin(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_timer_begin: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaEventRecord(c->ev_timer0, c->stream));
+    return NB_OK;
+}
+
+extern "C" int nb_timer_end(nb_ctx* c, float* elapsed_ms) {
+    if (!c || !elapsed_ms) return fail(NB_ERR_INVALID, "nb_timer_end: null");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaEventRecord(c->ev_timer1, c->stream));
+    NB_CUDA(cudaEventSynchronize(c->ev_timer1));
+    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    NB_CUDA(cudaEventElapsedTime(elapsed_ms, c->ev_timer0, c->ev_timer1));
+    return NB_OK;
+}
+
+extern "C" int nb_counters(nb_ctx* c, int64_t* kernel_launches, int64_t* force_evals, double* interactions) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_counters: null context");
+    if (kernel_launches) *kernel_launches = c->kernel_launches;
+    if (force_evals) *force_evals = c->force_evals;
+    if (interactions) *interactions = c->interactions;
+    return NB_OK;
+}
+
+extern "C" int nb_profile_forces(nb_ctx* c, int enable) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_profile_forces: null context");
+    c->profile = enable != 0;
+    c->prof_used = 0;
+    return NB_OK;
+}
+
+extern "C" int nb_profile_read(nb_ctx* c, int64_t* n_launches, double* total_ms) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_profile_read: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    double total = 0.0;
+    for (size_t k = 0; k + 1 < c->prof_used; k += 2) {
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, c->prof_events[k], c->prof_events[k + 1]));
+        total += ms;
+    }
+    if (n_launches) *n_launches = (int64_t)(c->prof_used / 2);
+    if (total_ms) *total_ms = total;
+    c->prof_used = 0;
+    return NB_OK;
+}

@@ -1,0 +1,280 @@
+"""Host-side mirror of the reference's ``nbody::Physics`` interface over the C-ABI.
+
+Same names, argument meaning and error behaviour as the statics of
+``src/systems/Physics.hpp`` (reference file:line in each docstring); every call goes
+through ``libnbody_b200.so`` (include/nbody_b200.h). There is no CPU fallback: if the
+CUDA library or a B200 is missing this module raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libnbody_b200.so")
+
+_dp = C.POINTER(C.c_double)
+_fp = C.POINTER(C.c_float)
+_bp = C.POINTER(C.c_uint8)
+
+
+class NbodyError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"nbody_b200 status {status}: {message}")
+        self.status = status
+
+
+class Config(C.Structure):
+    """Physics fields of the reference's Config singleton (src/core/Config.hpp:13-29)."""
+    _fields_ = [("g", C.c_double), ("softening", C.c_float), ("max_speed", C.c_float),
+                ("integrator", C.c_int32), ("max_substep", C.c_float), ("max_substeps_per_frame", C.c_int32)]
+
+
+class _Diag(C.Structure):
+    _fields_ = [("kinetic", C.c_double), ("potential", C.c_double), ("energy", C.c_double),
+                ("momentum", C.c_double * 3), ("com", C.c_double * 3), ("total_mass", C.c_double),
+                ("ok", C.c_int32), ("_pad", C.c_int32)]
+
+
+class Diagnostics:
+    """Physics::Diagnostics (Physics.hpp:22-30)."""
+
+    def __init__(self, d):
+        self.kinetic = d.kinetic
+        self.potential = d.potential
+        self.energy = d.energy
+        self.momentum = np.array(d.momentum[:])
+        self.com = np.array(d.com[:])
+        self.total_mass = d.total_mass
+        self.ok = bool(d.ok)
+
+    def as_reference_array(self):
+        """[KE, PE, E, Px, Py, COMx, COMy, M] — the 2-D field order of Physics.hpp:22-30."""
+        return np.array([self.kinetic, self.potential, self.energy, self.momentum[0], self.momentum[1],
+                         self.com[0], self.com[1], self.total_mass])
+
+
+EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
+           "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_download",
+           "nb_download3", "nb_num_bodies", "nb_local_range", "nb_compute_gravity", "nb_integrate", "nb_step",
+           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum",
+           "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
+           "nb_profile_forces", "nb_profile_read"]
+
+PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
+
+_lib = None
+
+
+def load_library(path=LIB_PATH):
+    """dlopen the C-ABI library; fails loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise NbodyError(-1, f"{path} not found: build it with raylib-nbody_b200/csrc/build.sh "
+                             "(or __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(path)
+    L.nb_last_error.restype = C.c_char_p
+    L.nb_num_bodies.restype = C.c_int64
+    L.nb_num_bodies.argtypes = [C.c_void_p]
+    L.nb_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    L.nb_create_sharded.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.nb_destroy.argtypes = [C.c_void_p]
+    L.nb_destroy.restype = None
+    L.nb_upload.argtypes = [C.c_void_p, C.c_int64, _dp, _dp, _fp, _bp]
+    L.nb_upload3.argtypes = [C.c_void_p, C.c_int64, _dp, _dp, _fp, _bp]
+    L.nb_download.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    L.nb_download3.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
+    L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
+    L.nb_default_config.argtypes = [C.POINTER(Config)]
+    L.nb_set_precision.argtypes = [C.c_void_p, C.c_int]
+    L.nb_local_range.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.nb_compute_gravity.argtypes = [C.c_void_p]
+    L.nb_integrate.argtypes = [C.c_void_p, C.c_float]
+    L.nb_step.argtypes = [C.c_void_p, C.c_float, C.c_int64]
+    L.nb_step_with_diagnostics.argtypes = [C.c_void_p, C.c_float, C.c_int64]
+    L.nb_step_diagnostics.argtypes = [C.c_void_p, C.POINTER(_Diag)]
+    L.nb_compute_diagnostics.argtypes = [C.c_void_p, C.POINTER(_Diag)]
+    L.nb_zero_net_momentum.argtypes = [C.c_void_p]
+    L.nb_substep_plan.argtypes = [C.c_float, C.c_float, C.c_int32, _fp]
+    L.nb_reset_scenario.argtypes = [C.c_void_p]
+    L.nb_synchronize.argtypes = [C.c_void_p]
+    L.nb_timer_begin.argtypes = [C.c_void_p]
+    L.nb_timer_end.argtypes = [C.c_void_p, _fp]
+    L.nb_counters.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), _dp]
+    L.nb_profile_forces.argtypes = [C.c_void_p, C.c_int]
+    L.nb_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_int64), _dp]
+    L.nb_comm_unique_id.argtypes = [C.c_void_p]
+    _lib = L
+    return L
+
+
+def default_config():
+    """Defaults of src/core/Constants.hpp:86-100 and Config.hpp:25."""
+    cfg = Config()
+    _check(load_library().nb_default_config(C.byref(cfg)))
+    return cfg
+
+
+def _check(status):
+    if status != 0:
+        raise NbodyError(status, (load_library().nb_last_error() or b"").decode())
+
+
+def substep_plan(dt, max_substep, max_substeps_per_frame):
+    """(nSteps, dtSub) of Physics.hpp:268-271."""
+    out = C.c_float()
+    n = load_library().nb_substep_plan(C.c_float(dt), C.c_float(max_substep), C.c_int32(max_substeps_per_frame),
+                                       C.byref(out))
+    return n, out.value
+
+
+def dt_eff(fixed_dt, time_scale):
+    """dtEff = baseDt * max(0, time_scale) in float, Physics.hpp:54-55 with use_fixed_dt."""
+    return float(np.float32(fixed_dt) * max(np.float32(0.0), np.float32(time_scale)))
+
+
+def comm_unique_id():
+    buf = C.create_string_buffer(128)
+    _check(load_library().nb_comm_unique_id(buf))
+    return buf.raw
+
+
+class Physics:
+    """Device-resident world state with the reference's Physics entry points."""
+
+    def __init__(self, device=0, rank=0, world=1, unique_id=None):
+        L = load_library()
+        self._L = L
+        self._h = C.c_void_p()
+        if world > 1:
+            _check(L.nb_create_sharded(device, rank, world, unique_id, C.byref(self._h)))
+        else:
+            _check(L.nb_create(device, C.byref(self._h)))
+        self.rank, self.world = rank, world
+        self.dim = 2
+
+    def close(self):
+        if self._h:
+            self._L.nb_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- Config singleton ------------------------------------------------------------
+    def set_config(self, cfg=None, **fields):
+        if cfg is None:
+            cfg = self.get_config()
+        for k, v in fields.items():
+            setattr(cfg, k, v)
+        _check(self._L.nb_set_config(self._h, C.byref(cfg)))
+        return cfg
+
+    def get_config(self):
+        cfg = Config()
+        _check(self._L.nb_get_config(self._h, C.byref(cfg)))
+        return cfg
+
+    def set_precision(self, mode):
+        """PRECISION_AUTO / PRECISION_FP32 / PRECISION_FP64_EXACT (include/nbody_b200.h)."""
+        _check(self._L.nb_set_precision(self._h, int(mode)))
+
+    # ---- bodies ------------------------------------------------------------------------
+    def upload(self, pos, vel, mass, pinned=None):
+        """Replace all bodies; pos/vel are (n,2) [reference layout] or (n,3) float64."""
+        pos = np.ascontiguousarray(pos, np.float64)
+        vel = np.ascontiguousarray(vel, np.float64)
+        mass = np.ascontiguousarray(mass, np.float32)
+        n, dim = (pos.shape[0], pos.shape[1]) if pos.ndim == 2 else (0, 2)
+        if pos.ndim != 2 or dim not in (2, 3) or vel.shape != pos.shape or mass.shape != (n,):
+            raise NbodyError(1, "upload: pos/vel must be (n,2) or (n,3), mass (n,)")
+        pin = None
+        if pinned is not None:
+            pin = np.ascontiguousarray(pinned, np.uint8)
+            if pin.shape != (n,):
+                raise NbodyError(1, "upload: pinned must be (n,)")
+        fn = self._L.nb_upload if dim == 2 else self._L.nb_upload3
+        _check(fn(self._h, n, pos.ctypes.data_as(_dp), vel.ctypes.data_as(_dp), mass.ctypes.data_as(_fp),
+                  None if pin is None else pin.ctypes.data_as(_bp)))
+        self.dim = dim
+
+    def download(self, pos=True, vel=True, acc=True):
+        """(pos, vel, acc) as (n,dim) float64; a sharded context fills its own rows only."""
+        n = self.num_bodies()
+        out = [np.zeros((n, self.dim)) if want else None for want in (pos, vel, acc)]
+        fn = self._L.nb_download if self.dim == 2 else self._L.nb_download3
+        _check(fn(self._h, *[None if a is None else a.ctypes.data_as(_dp) for a in out]))
+        return tuple(out)
+
+    def num_bodies(self):
+        return int(self._L.nb_num_bodies(self._h))
+
+    def local_range(self):
+        lo, hi = C.c_int64(), C.c_int64()
+        _check(self._L.nb_local_range(self._h, C.byref(lo), C.byref(hi)))
+        return lo.value, hi.value
+
+    # ---- reference statics ---------------------------------------------------------------
+    def compute_gravity(self):
+        """Physics::compute_gravity, Physics.hpp:183-261 (direct-sum branch)."""
+        _check(self._L.nb_compute_gravity(self._h))
+
+    def integrate(self, dt):
+        """Physics::integrate, Physics.hpp:263-327."""
+        _check(self._L.nb_integrate(self._h, C.c_float(dt)))
+
+    def compute_diagnostics(self):
+        """Physics::compute_diagnostics, Physics.hpp:117-177."""
+        d = _Diag()
+        _check(self._L.nb_compute_diagnostics(self._h, C.byref(d)))
+        return Diagnostics(d)
+
+    def zero_net_momentum(self):
+        """Physics::zero_net_momentum, Physics.hpp:66-85."""
+        _check(self._L.nb_zero_net_momentum(self._h))
+
+    def reset_scenario(self):
+        """Physics::reset_scenario, Physics.hpp:87-115 (three-body seed)."""
+        _check(self._L.nb_reset_scenario(self._h))
+        self.dim = 2
+
+    def step(self, dt, n_frames=1, diagnostics=False):
+        """n_frames x (gravity system + integrate system), Physics.hpp:45-57 — fused path."""
+        fn = self._L.nb_step_with_diagnostics if diagnostics else self._L.nb_step
+        _check(fn(self._h, C.c_float(dt), n_frames))
+
+    def step_diagnostics(self):
+        d = _Diag()
+        _check(self._L.nb_step_diagnostics(self._h, C.byref(d)))
+        return Diagnostics(d)
+
+    # ---- measurement -------------------------------------------------------------------
+    def synchronize(self):
+        _check(self._L.nb_synchronize(self._h))
+
+    def timer_begin(self):
+        _check(self._L.nb_timer_begin(self._h))
+
+    def timer_end(self):
+        ms = C.c_float()
+        _check(self._L.nb_timer_end(self._h, C.byref(ms)))
+        return ms.value
+
+    def counters(self):
+        k, f, x = C.c_int64(), C.c_int64(), C.c_double()
+        _check(self._L.nb_counters(self._h, C.byref(k), C.byref(f), C.byref(x)))
+        return dict(kernel_launches=k.value, force_evals=f.value, interactions=x.value)
+
+    def profile_forces(self, enable=True):
+        _check(self._L.nb_profile_forces(self._h, int(enable)))
+
+    def profile_read(self):
+        n, ms = C.c_int64(), C.c_double()
+        _check(self._L.nb_profile_read(self._h, C.byref(n), C.byref(ms)))
+        return n.value, ms.value
