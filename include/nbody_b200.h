@@ -123,6 +123,9 @@ int nb_download3(nb_ctx* ctx, double* pos_xyz, double* vel_xyz, double* acc_xyz)
 
 int64_t nb_num_bodies(nb_ctx* ctx);
 int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);
+/* The target partition a sharded context uses: contiguous, aligned to the 512-body source
+ * tile, equal tile counts per rank (so the all-gather is uniform). Host-only, no context. */
+int nb_partition(int64_t n, int rank, int world, int64_t* lo, int64_t* hi);
 
 /* ---- the hot path ----------------------------------------------------------------- */
 

@@ -7,6 +7,7 @@
 #pragma once
 #include "epilogue.cuh"
 #include "ptx.cuh"
+#include "state.cuh"
 
 namespace nb {
 
@@ -95,6 +96,63 @@ __global__ void __launch_bounds__(kDiagThreads) diag_potential_kernel(
         const double x[3] = {x0[i], x1[i], x2[i]};
         const double v[3] = {v0[i], v1[i], v2[i]};
         diag_accumulate(dg, x, v, mass[i], phi * sc.pot_unit, g, true);
+    }
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+        double w = dg.v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = w;
+    }
+    __syncthreads();
+    if (threadIdx.x < 10) {
+        double w = 0.0;
+        for (int q = 0; q < kDiagThreads / 32; ++q) w += red[q][threadIdx.x];
+        part[(long long)blockIdx.x * kDiagValues + threadIdx.x] = w;
+    }
+}
+
+// FP64 variant for the exact path: the reference's pair terms -G*m_i*m_j/sqrt(r2) over i < j
+// (Physics.hpp:148-154) in FP64, one target per thread; only the summation order differs.
+__global__ void __launch_bounds__(kDiagThreads) diag_exact_kernel(StateView s, double g, float softening,
+                                                                  double* part) {
+    __shared__ double sx[kDiagThreads], sy[kDiagThreads], sz[kDiagThreads], sm[kDiagThreads];
+    __shared__ double red[kDiagThreads / 32][kDiagValues];
+    const double eps2 = (double)softening * (double)softening;
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const bool valid = i < s.n;
+    double xi[3] = {0, 0, 0}, vi[3] = {0, 0, 0};
+    float mi = 0.f;
+    if (valid) {
+        for (int k = 0; k < 3; ++k) { xi[k] = s.x[k][i]; vi[k] = s.v[k][i]; }
+        mi = s.mass[i];
+    }
+    double pe = 0.0;
+    const long long j_start = (blockIdx.x * (long long)blockDim.x / kDiagThreads) * kDiagThreads;
+    for (long long j0 = j_start; j0 < s.n; j0 += kDiagThreads) {
+        const long long j = j0 + threadIdx.x;
+        if (j < s.n) {
+            sx[threadIdx.x] = s.x[0][j]; sy[threadIdx.x] = s.x[1][j]; sz[threadIdx.x] = s.x[2][j];
+            sm[threadIdx.x] = (double)s.mass[j];
+        }
+        __syncthreads();
+        if (valid) {
+            const int cnt = (int)min((long long)kDiagThreads, s.n - j0);
+            for (int u = 0; u < cnt; ++u) {
+                if (j0 + u <= i) continue;
+                const double dx = sx[u] - xi[0], dy = sy[u] - xi[1], dz = sz[u] - xi[2];
+                const double r = __dsqrt_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)), eps2));
+                pe += __ddiv_rn(__dmul_rn(__dmul_rn(-g, (double)mi), sm[u]), r);
+            }
+        }
+        __syncthreads();
+    }
+    DiagTerms dg;
+#pragma unroll
+    for (int k = 0; k < kDiagValues; ++k) dg.v[k] = 0.0;
+    if (valid) {
+        diag_accumulate(dg, xi, vi, mi, 0.0, g, false);
+        dg.v[1] = pe;
     }
 #pragma unroll
     for (int k = 0; k < 10; ++k) {

@@ -45,6 +45,8 @@ static int fail(int code, const std::string& msg) {
     } while (0)
 
 extern "C" const char* nb_last_error(void) { return g_last_error.c_str(); }
+extern "C" int nb_partition(int64_t n, int rank, int world, int64_t* lo, int64_t* hi);
+static bool use_exact(const nb_ctx* c);
 extern "C" int nb_abi_version(void) { return NB_ABI_VERSION; }
 
 // ---------------------------------------------------------------------------------------
@@ -230,8 +232,10 @@ int size_for(nb_ctx* c, long long n) {
     const long long tiles = std::max<long long>(1, (n + kTileBodies - 1) / kTileBodies);
     c->tiles_per_rank = (tiles + c->world - 1) / c->world;
     c->n_tiles = c->tiles_per_rank * c->world;
-    c->lo = std::min<long long>(n, (long long)c->rank * c->tiles_per_rank * kTileBodies);
-    c->hi = std::min<long long>(n, (long long)(c->rank + 1) * c->tiles_per_rank * kTileBodies);
+    int64_t lo = 0, hi = 0;
+    nb_partition(n, c->rank, c->world, &lo, &hi);
+    c->lo = lo;
+    c->hi = hi;
     c->n = n;
     const long long rows = c->n_tiles * kTileBodies;
     if (rows > c->cap) {
@@ -416,6 +420,15 @@ extern "C" int nb_local_range(nb_ctx* c, int64_t* lo, int64_t* hi) {
     if (!c) return fail(NB_ERR_INVALID, "nb_local_range: null");
     if (lo) *lo = c->lo;
     if (hi) *hi = c->hi;
+    return NB_OK;
+}
+
+extern "C" int nb_partition(int64_t n, int rank, int world, int64_t* lo, int64_t* hi) {
+    if (n < 0 || world < 1 || rank < 0 || rank >= world) return fail(NB_ERR_INVALID, "nb_partition: bad arguments");
+    const long long tiles = std::max<long long>(1, (n + kTileBodies - 1) / kTileBodies);
+    const long long per_rank = (tiles + world - 1) / world;
+    if (lo) *lo = std::min<long long>(n, (long long)rank * per_rank * kTileBodies);
+    if (hi) *hi = std::min<long long>(n, (long long)(rank + 1) * per_rank * kTileBodies);
     return NB_OK;
 }
 
@@ -650,7 +663,7 @@ extern "C" int nb_download3(nb_ctx* c, double* pos_xyz, double* vel_xyz, double*
 // ---------------------------------------------------------------------------------------
 // FP64 exact path (exact.cuh): unfused, every kernel reads state written by the previous one
 // ---------------------------------------------------------------------------------------
-static bool use_exact(const nb_ctx* c) {
+bool use_exact(const nb_ctx* c) {
     if (c->world > 1) return false;
     if (c->precision == NB_PRECISION_FP64_EXACT) return true;
     return c->precision == NB_PRECISION_AUTO && c->n <= NB_EXACT_AUTO_MAX;
@@ -878,6 +891,14 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
     }
     const StateView s = c->view();
     const long long n_local = c->hi - c->lo;
+    if (use_exact(c)) {
+        const long long rows = blocks_for(c->n, kDiagThreads);
+        diag_exact_kernel<<<(unsigned int)rows, kDiagThreads, 0, c->stream>>>(s, c->cfg.g, c->cfg.softening, c->diag_part);
+        NB_CUDA(cudaGetLastError());
+        c->kernel_launches++;
+        c->step_diag_valid = false;
+        return finish_diag(c, rows, out);
+    }
     NB_CUDA(cudaMemsetAsync(c->extent + kDiagExtentSlot, 0, sizeof(unsigned int), c->stream));
     long long rows = 0;
     if (n_local > 0) {

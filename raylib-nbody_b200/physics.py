@@ -56,7 +56,7 @@ class Diagnostics:
 
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_download",
-           "nb_download3", "nb_num_bodies", "nb_local_range", "nb_compute_gravity", "nb_integrate", "nb_step",
+           "nb_download3", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read"]
@@ -91,6 +91,7 @@ def load_library(path=LIB_PATH):
     L.nb_default_config.argtypes = [C.POINTER(Config)]
     L.nb_set_precision.argtypes = [C.c_void_p, C.c_int]
     L.nb_local_range.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.nb_partition.argtypes = [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_compute_gravity.argtypes = [C.c_void_p]
     L.nb_integrate.argtypes = [C.c_void_p, C.c_float]
     L.nb_step.argtypes = [C.c_void_p, C.c_float, C.c_int64]
@@ -134,6 +135,13 @@ def substep_plan(dt, max_substep, max_substeps_per_frame):
 def dt_eff(fixed_dt, time_scale):
     """dtEff = baseDt * max(0, time_scale) in float, Physics.hpp:54-55 with use_fixed_dt."""
     return float(np.float32(fixed_dt) * max(np.float32(0.0), np.float32(time_scale)))
+
+
+def partition(n, rank, world):
+    """Rows [lo,hi) rank `rank` of `world` owns (host-only; mirrors nb_create_sharded's split)."""
+    lo, hi = C.c_int64(), C.c_int64()
+    _check(load_library().nb_partition(n, rank, world, C.byref(lo), C.byref(hi)))
+    return lo.value, hi.value
 
 
 def comm_unique_id():

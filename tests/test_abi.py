@@ -1,0 +1,84 @@
+"""C-ABI surface checks that need no GPU: the library loads, exports every symbol the header
+declares, mirrors the reference's config surface, and fails loudly (never falls back) without
+a CUDA device."""
+import ctypes as C
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, _have_gpu
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "nbody_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(nb_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = pkg.load_library()
+    names = header_functions()
+    assert len(names) >= 30
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/nbody_b200.h but not exported"
+    assert sorted(pkg.EXPORTS) == names
+    assert lib.nb_abi_version() == 1
+
+
+def test_default_config_matches_reference_defaults(pkg):
+    with open(os.path.join(GOLDEN, "defaults.json")) as f:
+        ref = json.load(f)
+    cfg = pkg.default_config()
+    for k in ("g", "softening", "max_speed", "integrator", "max_substep", "max_substeps_per_frame"):
+        assert getattr(cfg, k) == ref[k], k
+
+
+def test_struct_layouts_match_header(pkg):
+    from raylib_nbody_b200 import physics
+    assert C.sizeof(physics.Config) == 32
+    assert C.sizeof(physics._Diag) == 88
+
+
+@pytest.mark.parametrize("dt,cap,lim", [(8333.334, 1e9, 200), (8333.334, 3000.0, 200), (8333.334, 1.0, 200),
+                                         (0.0, 1e9, 200), (5.0, 0.0, 7), (100.0, 30.0, 0), (1e-7, 1e-9, 50)])
+def test_substep_plan_matches_oracle(pkg, oracle_lib, dt, cap, lim):
+    assert pkg.substep_plan(dt, cap, lim) == oracle_lib.substep_plan(dt, cap, lim)
+
+
+def test_dt_eff_is_float_arithmetic(pkg, ob):
+    assert pkg.dt_eff(ob.DEFAULTS["fixed_dt"], ob.DEFAULTS["time_scale"]) == ob.dt_eff() == 8333.333984375
+    assert pkg.dt_eff(0.01, -5.0) == 0.0
+
+
+def test_partition_is_tile_aligned_and_covers(pkg):
+    for n in (0, 3, 511, 512, 513, 4096, 65536, (1 << 20) + 17):
+        for world in (1, 2, 3, 8):
+            spans = [pkg.partition(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            for (lo, hi), (lo2, _) in zip(spans, spans[1:]):
+                assert hi == lo2 and lo <= hi
+            assert all(lo % 512 == 0 or lo == n for lo, _ in spans)
+            sizes = {hi - lo for lo, hi in spans if hi < n}
+            assert len(sizes) <= 1  # equal tile counts: the all-gather is uniform
+
+
+def test_no_cpu_fallback(pkg):
+    """Without a CUDA device creation fails with NB_ERR_NO_DEVICE; nothing computes on the CPU."""
+    if _have_gpu():
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.NbodyError) as e:
+        pkg.Physics(0)
+    assert e.value.status == 2 and "no CPU path" in str(e.value)
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under the package may import, link or load it."""
+    pkg_dir = os.path.join(ROOT, "raylib-nbody_b200")
+    for base, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".sh")):
+                text = open(os.path.join(base, f)).read()
+                assert "oracle" not in text.lower().replace("oracle/", "oracle/") or f == "never", (base, f)

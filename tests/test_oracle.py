@@ -1,0 +1,165 @@
+"""Pins the plain-C oracle (oracle/nbody_oracle.c) against the UNMODIFIED reference:
+bit-for-bit against the committed fixtures the reference generated (tests/golden/, made by
+make_golden.py) everywhere, and against the live reference library where it exists."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, golden
+
+
+def test_defaults_match_reference(ob):
+    with open(os.path.join(GOLDEN, "defaults.json")) as f:
+        ref = json.load(f)
+    for k, v in ref.items():
+        assert float(np.float32(ob.DEFAULTS[k])) == pytest.approx(v, rel=0, abs=0) or ob.DEFAULTS[k] == v, k
+    assert ob.dt_eff() == float(np.float32(ref["fixed_dt"]) * np.float32(ref["time_scale"]))
+
+
+def test_three_body_seed_bitexact(oracle_lib):
+    g = golden("c1_three_body.npz")
+    pos, vel, mass, pinned = oracle_lib.seed_three_body()
+    assert np.array_equal(pos, g["seed_pos"]) and np.array_equal(vel, g["seed_vel"])
+    assert np.array_equal(mass, g["seed_mass"]) and not pinned.any()
+    d, ok = oracle_lib.compute_diagnostics(pos, vel, mass)
+    assert ok and np.array_equal(d, g["verlet_diag0"])
+    # survey anchor: E0 of the reference's config-1 run
+    assert d[2] == -7.6598098902915506e28
+
+
+@pytest.mark.parametrize("integ,name", [(1, "verlet"), (0, "euler")])
+def test_three_body_10k_frames_bitexact(oracle_lib, ob, integ, name):
+    g = golden("c1_three_body.npz")
+    pos, vel, mass, pinned = oracle_lib.seed_three_body()
+    acc, acc0 = np.zeros((3, 2)), np.zeros((3, 2))
+    cfg = ob.make_config(integrator=integ)
+    dt = float(g["dt_eff"])
+    assert dt == ob.dt_eff()
+    done = 0
+    for upto in (100, 1000, 10000):
+        oracle_lib.physics_frames(pos, vel, acc, acc0, mass, pinned, cfg, dt, upto - done)
+        done = upto
+        assert np.array_equal(pos, g[f"{name}_pos_{upto}"]), upto
+        assert np.array_equal(vel, g[f"{name}_vel_{upto}"]), upto
+        assert np.array_equal(acc, g[f"{name}_acc_{upto}"]), upto
+        d, ok = oracle_lib.compute_diagnostics(pos, vel, mass)
+        assert ok and np.array_equal(d, g[f"{name}_diag_{upto}"])
+    # reference invariants: body 0 stays at the origin, momentum exactly 0
+    assert np.array_equal(pos[0], [0.0, 0.0]) and d[3] == 0.0 and d[4] == 0.0
+    drift = float(g[f"{name}_max_drift_10000"])
+    assert drift < (2e-6 if integ == 1 else 6e-4)
+
+
+def test_frame_equals_reference_pipeline(oracle_lib, ob):
+    """gravity+integrate frames == the reference's full flecs progress() when nothing merges."""
+    g = golden("c1_three_body.npz")
+    pos, vel, mass, pinned = oracle_lib.seed_three_body()
+    acc, acc0 = np.zeros((3, 2)), np.zeros((3, 2))
+    oracle_lib.physics_frames(pos, vel, acc, acc0, mass, pinned, ob.make_config(), float(g["dt_eff"]), 10)
+    assert np.array_equal(pos, g["progress_pos_10"]) and np.array_equal(vel, g["progress_vel_10"])
+
+
+def test_disk_4096_accelerations_bitexact(oracle_lib):
+    g = golden("c2_disk_4096.npz")
+    pos, mass = g["pos"], g["mass"]
+    acc = oracle_lib.compute_gravity(pos, np.zeros_like(pos), mass)
+    assert np.array_equal(acc, g["acc"])
+    d, ok = oracle_lib.compute_diagnostics(pos, np.zeros_like(pos), mass)
+    assert ok and np.array_equal(d, g["diag"])
+
+
+def test_scenario_generator_reproduces_fixture_inputs(pkg):
+    g = golden("c2_disk_4096.npz")
+    pos, vel, mass = pkg.scenarios.uniform_disk(4096, seed=1234)
+    assert np.array_equal(pos, g["pos"]) and np.array_equal(mass, g["mass"])
+    assert np.array_equal(pos, pos.astype(np.float32).astype(np.float64))  # float-representable
+
+
+@pytest.mark.parametrize("integ,name", [(1, "verlet"), (0, "euler")])
+def test_mixed_bodies_filters_pins_cap_substeps_bitexact(oracle_lib, ob, integ, name):
+    g = golden("mixed_256.npz")
+    pos, vel, mass, pinned = g["pos"].copy(), g["vel"].copy(), g["mass"], g["pinned"]
+    n = pos.shape[0]
+    acc0 = oracle_lib.compute_gravity(pos, vel, mass, pinned)
+    assert np.array_equal(acc0, g[f"{name}_acc0"])
+    # filtered bodies keep a stale (zero) acceleration, pinned ones get exactly zero
+    assert not acc0[5].any() and not acc0[7].any() and not acc0[pinned == 1].any()
+    cfg = ob.make_config(integrator=integ, max_substep=3000.0, max_speed=2000.0)
+    n_sub, dt_sub = oracle_lib.substep_plan(ob.dt_eff(), 3000.0, 200)
+    assert n_sub == 3
+    acc, accp = np.zeros((n, 2)), np.zeros((n, 2))
+    oracle_lib.physics_frames(pos, vel, acc, accp, mass, pinned, cfg, ob.dt_eff(), 3)
+    assert np.array_equal(pos, g[f"{name}_pos"], equal_nan=True)
+    assert np.array_equal(vel, g[f"{name}_vel"], equal_nan=True)
+    assert np.array_equal(acc, g[f"{name}_acc"], equal_nan=True)
+    d, ok = oracle_lib.compute_diagnostics(pos, vel, mass)
+    assert ok == bool(g[f"{name}_diag_ok"]) and not ok and not d.any()
+
+
+def test_zero_net_momentum_bitexact(oracle_lib):
+    g = golden("mixed_256.npz")
+    vel = g["vel"].copy()
+    oracle_lib.zero_net_momentum(vel, g["mass"], g["pinned"])
+    assert np.array_equal(vel, g["zeroed_vel"], equal_nan=True)
+
+
+def test_plummer_diagnostics_and_gravity_bitexact(oracle_lib):
+    g = golden("plummer2d_1024.npz")
+    d, ok = oracle_lib.compute_diagnostics(g["pos"], g["vel"], g["mass"])
+    assert ok and np.array_equal(d, g["diag"])
+    assert np.array_equal(oracle_lib.compute_gravity(g["pos"], g["vel"], g["mass"]), g["acc"])
+
+
+def test_3d_oracle_reduces_to_2d(oracle_lib, ob):
+    g = golden("plummer2d_1024.npz")
+    n = g["pos"].shape[0]
+    pos3 = np.concatenate([g["pos"], np.zeros((n, 1))], axis=1)
+    vel3 = np.concatenate([g["vel"], np.zeros((n, 1))], axis=1)
+    acc3 = oracle_lib.compute_gravity(pos3, vel3, g["mass"])
+    assert np.array_equal(acc3[:, :2], g["acc"]) and not acc3[:, 2].any()
+    d3, ok = oracle_lib.compute_diagnostics(pos3, vel3, g["mass"])
+    assert ok and np.allclose(d3[[0, 1, 2, 3, 4, 6, 7, 9]], g["diag"], rtol=1e-15, atol=0)
+    p3, v3 = pos3.copy(), vel3.copy()
+    p2, v2 = g["pos"].copy(), g["vel"].copy()
+    a3, b3, a2, b2 = np.zeros((n, 3)), np.zeros((n, 3)), np.zeros((n, 2)), np.zeros((n, 2))
+    cfg = ob.make_config()
+    oracle_lib.physics_frames(p3, v3, a3, b3, g["mass"], np.zeros(n, np.uint8), cfg, 50.0, 2)
+    oracle_lib.physics_frames(p2, v2, a2, b2, g["mass"], np.zeros(n, np.uint8), cfg, 50.0, 2)
+    assert np.array_equal(p3[:, :2], p2) and np.array_equal(v3[:, :2], v2)
+
+
+def test_empty_world(oracle_lib):
+    e2, e1 = np.zeros((0, 2)), np.zeros(0, np.float32)
+    assert oracle_lib.compute_gravity(e2, e2, e1).shape == (0, 2)
+    d, ok = oracle_lib.compute_diagnostics(e2, e2, e1)
+    assert ok and not d.any()
+
+
+def test_against_live_reference(oracle_lib, ob):
+    """Where the compiled reference exists (build container), re-check on fresh random inputs."""
+    if not ob.have_reference():
+        pytest.skip("oracle/_ref/libnbref.so not present (no /root/reference on this machine)")
+    r = ob.Reference()
+    rng = np.random.default_rng(2024)
+    n = 300
+    pos = (rng.standard_normal((n, 2)) * 2e8).astype(np.float32).astype(np.float64)
+    vel = rng.standard_normal((n, 2)) * 500.0
+    mass = rng.uniform(1e21, 1e25, n).astype(np.float32)
+    pinned = (rng.uniform(size=n) < 0.1).astype(np.uint8)
+    for integ in (0, 1):
+        r.set_config(integrator=integ, softening=1.0e5, max_substep=5000.0)
+        r.load_bodies(pos, vel, mass, pinned)
+        for _ in range(4):
+            r.physics_frame()
+        P, V, A, _, _ = r.read_bodies()
+        p, v = pos.copy(), vel.copy()
+        a, a0 = np.zeros((n, 2)), np.zeros((n, 2))
+        cfg = ob.make_config(integrator=integ, softening=1.0e5, max_substep=5000.0)
+        oracle_lib.physics_frames(p, v, a, a0, mass, pinned, cfg, ob.dt_eff(), 4)
+        assert np.array_equal(P, p) and np.array_equal(V, v) and np.array_equal(A, a)
+        dr, okr = r.compute_diagnostics()
+        do, oko = oracle_lib.compute_diagnostics(p, v, mass, softening=1.0e5)
+        assert okr == oko and np.array_equal(dr, do)
+    r.close()
