@@ -116,6 +116,14 @@ int nb_upload(nb_ctx* ctx, int64_t n, const double* pos_xy, const double* vel_xy
 int nb_upload3(nb_ctx* ctx, int64_t n, const double* pos_xyz, const double* vel_xyz, const float* mass,
                const uint8_t* pinned);
 
+/* Same, additionally taking the Acceleration components the caller holds (may be NULL). When
+ * given, the caller asserts they equal a(x) for these positions — true for components this
+ * library scattered back after the previous frame, the situation the reference's comment at
+ * Physics.hpp:324 describes — so a Verlet frame needs one force evaluation instead of two.
+ * dim is 2 (reference layout) or 3. */
+int nb_upload_state(nb_ctx* ctx, int64_t n, int dim, const double* pos, const double* vel, const double* acc,
+                    const float* mass, const uint8_t* pinned);
+
 /* Scatter back (Physics.hpp:260 and the in-place writes of :276-323). Any pointer may be
  * NULL. Arrays are sized for all n bodies; a sharded context fills rows [lo,hi) only. */
 int nb_download(nb_ctx* ctx, double* pos_xy, double* vel_xy, double* acc_xy);
@@ -171,6 +179,13 @@ int nb_synchronize(nb_ctx* ctx);
 /* CUDA events on the library's own stream around whatever is enqueued between them. */
 int nb_timer_begin(nb_ctx* ctx);
 int nb_timer_end(nb_ctx* ctx, float* elapsed_ms); /* synchronises */
+/* SM count, compute capability and max SM clock (kHz) of the context's device. */
+int nb_device_info(nb_ctx* ctx, int* sm_count, int* cc_major, int* cc_minor, int* sm_clock_khz);
+/* Evicts L2 by overwriting a 256 MiB scratch buffer on the library's stream (benchmark hygiene). */
+int nb_flush_l2(nb_ctx* ctx);
+/* Page-locked host memory for callers that want full-speed uploads/downloads. */
+int nb_alloc_pinned(size_t bytes, void** out);
+int nb_free_pinned(void* p);
 /* Kernels launched / force evaluations / body-body interactions since creation. */
 int nb_counters(nb_ctx* ctx, int64_t* kernel_launches, int64_t* force_evals, double* interactions);
 /* Device-time of the force kernels alone since the last call (events around every force

@@ -4,7 +4,7 @@ Only the hot path lives here: the CUDA kernels + C-ABI (csrc/, libnbody_b200.so)
 host-side mirror of the reference's Physics interface (physics.py). Import through
 ``__graft_entry__.load_package()`` (the directory name is not a Python identifier).
 """
-from .physics import (Config, Diagnostics, NbodyError, Physics, comm_unique_id, default_config, partition, dt_eff,  # noqa: F401
+from .physics import (Config, Diagnostics, NbodyError, Physics, comm_unique_id, default_config, partition, pinned_array, dt_eff,  # noqa: F401
                       load_library, substep_plan, EXPORTS, LIB_PATH, PRECISION_AUTO, PRECISION_FP32,
                       PRECISION_FP64_EXACT)
 from . import scenarios, sharded  # noqa: F401

@@ -67,6 +67,7 @@ struct nb_ctx {
     double* totals = nullptr;           // device scratch for fixed-order final sums (64 doubles)
     double* h_totals = nullptr;         // pinned host mirror
     float4* dpk = nullptr;              // stand-alone diagnostics pack
+    void* l2_scratch = nullptr;         // 256 MiB, nb_flush_l2
     void* staging = nullptr;            // device staging for AoS uploads/downloads
     size_t staging_bytes = 0;
 

@@ -185,15 +185,15 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
 namespace {
 
 // staging: [pos dim*n doubles][vel dim*n doubles]; rows [0,n) of the SoA state
-__global__ void __launch_bounds__(256) unpack_aos_kernel(const double* pos, const double* vel, int dim, long long n,
-                                                         StateView s) {
+__global__ void __launch_bounds__(256) unpack_aos_kernel(const double* pos, const double* vel, const double* acc,
+                                                         int dim, long long n, StateView s) {
     const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= n) return;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         s.x[k][i] = k < dim ? pos[i * dim + k] : 0.0;
         s.v[k][i] = k < dim ? vel[i * dim + k] : 0.0;
-        s.a[k][i] = 0.0;   // fresh entities start with Acceleration{0}, Physics.hpp:97
+        s.a[k][i] = (acc && k < dim) ? acc[i * dim + k] : 0.0;  // fresh entities: Acceleration{0}, Physics.hpp:97
         s.a0[k][i] = 0.0;  // and PrevAcceleration{0}, :98
     }
 }
@@ -386,6 +386,7 @@ extern "C" void nb_destroy(nb_ctx* c) {
     if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     free_bodies(c);
     cudaFree(c->extent);
+    cudaFree(c->l2_scratch);
     cudaFree(c->totals);
     cudaFreeHost(c->h_totals);
     for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
@@ -595,7 +596,7 @@ int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
 // state upload / download
 // ---------------------------------------------------------------------------------------
 static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel, const float* mass,
-                      const uint8_t* pinned, int dim) {
+                      const uint8_t* pinned, int dim, const double* acc = nullptr) {
     if (!c) return fail(NB_ERR_INVALID, "nb_upload: null context");
     if (n < 0 || (n > 0 && (!pos || !vel || !mass))) return fail(NB_ERR_INVALID, "nb_upload: null array");
     NB_CUDA(cudaSetDevice(c->device));
@@ -608,16 +609,19 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
     c->step_diag_valid = false;
     if (n == 0) return NB_OK;
     const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n;
-    NB_TRY(ensure_staging(c, 2 * vec_bytes));
+    NB_TRY(ensure_staging(c, 3 * vec_bytes));
     double* d_pos = static_cast<double*>(c->staging);
     double* d_vel = d_pos + (size_t)dim * n;
+    double* d_acc = d_vel + (size_t)dim * n;
     NB_CUDA(cudaMemcpyAsync(d_pos, pos, vec_bytes, cudaMemcpyHostToDevice, c->stream));
     NB_CUDA(cudaMemcpyAsync(d_vel, vel, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+    if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc, vec_bytes, cudaMemcpyHostToDevice, c->stream));
     NB_CUDA(cudaMemcpyAsync(c->mass, mass, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
     if (pinned) NB_CUDA(cudaMemcpyAsync(c->pinned, pinned, (size_t)n, cudaMemcpyHostToDevice, c->stream));
-    unpack_aos_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_pos, d_vel, dim, n, c->view());
+    unpack_aos_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_pos, d_vel, acc ? d_acc : nullptr, dim, n, c->view());
     NB_CUDA(cudaGetLastError());
     c->kernel_launches++;
+    c->acc_valid = acc != nullptr;
     NB_TRY(prepare_packed(c));
     // the borrowed host arrays may be pageable: do not return while a copy could still read them
     NB_CUDA(cudaStreamSynchronize(c->stream));
@@ -631,6 +635,11 @@ extern "C" int nb_upload(nb_ctx* c, int64_t n, const double* pos_xy, const doubl
 extern "C" int nb_upload3(nb_ctx* c, int64_t n, const double* pos_xyz, const double* vel_xyz, const float* mass,
                           const uint8_t* pinned) {
     return upload_dim(c, n, pos_xyz, vel_xyz, mass, pinned, 3);
+}
+extern "C" int nb_upload_state(nb_ctx* c, int64_t n, int dim, const double* pos, const double* vel, const double* acc,
+                               const float* mass, const uint8_t* pinned) {
+    if (dim != 2 && dim != 3) return fail(NB_ERR_INVALID, "nb_upload_state: dim must be 2 or 3");
+    return upload_dim(c, n, pos, vel, mass, pinned, dim, acc);
 }
 
 static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int dim) {
@@ -1023,6 +1032,36 @@ extern "C" int nb_timer_end(nb_ctx* c, float* elapsed_ms) {
     NB_CUDA(cudaEventSynchronize(c->ev_timer1));
     NB_CUDA(cudaStreamSynchronize(c->comm_stream));
     NB_CUDA(cudaEventElapsedTime(elapsed_ms, c->ev_timer0, c->ev_timer1));
+    return NB_OK;
+}
+
+extern "C" int nb_device_info(nb_ctx* c, int* sm_count, int* cc_major, int* cc_minor, int* sm_clock_khz) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_device_info: null context");
+    int v = 0;
+    if (sm_count) *sm_count = c->sm_count;
+    if (cc_major) { NB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, c->device)); *cc_major = v; }
+    if (cc_minor) { NB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, c->device)); *cc_minor = v; }
+    if (sm_clock_khz) { NB_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrClockRate, c->device)); *sm_clock_khz = v; }
+    return NB_OK;
+}
+
+extern "C" int nb_flush_l2(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_flush_l2: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    const size_t bytes = (size_t)256 << 20;
+    if (!c->l2_scratch) NB_CUDA(cudaMalloc(&c->l2_scratch, bytes));
+    NB_CUDA(cudaMemsetAsync(c->l2_scratch, 0x5a, bytes, c->stream));
+    return NB_OK;
+}
+
+extern "C" int nb_alloc_pinned(size_t bytes, void** out) {
+    if (!out) return fail(NB_ERR_INVALID, "nb_alloc_pinned: null");
+    NB_CUDA(cudaMallocHost(out, bytes ? bytes : 1));
+    return NB_OK;
+}
+
+extern "C" int nb_free_pinned(void* p) {
+    if (p) NB_CUDA(cudaFreeHost(p));
     return NB_OK;
 }
 

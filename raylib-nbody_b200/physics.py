@@ -55,11 +55,11 @@ class Diagnostics:
 
 
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
-           "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_download",
+           "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
-           "nb_profile_forces", "nb_profile_read"]
+           "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
 
@@ -84,6 +84,11 @@ def load_library(path=LIB_PATH):
     L.nb_destroy.restype = None
     L.nb_upload.argtypes = [C.c_void_p, C.c_int64, _dp, _dp, _fp, _bp]
     L.nb_upload3.argtypes = [C.c_void_p, C.c_int64, _dp, _dp, _fp, _bp]
+    L.nb_upload_state.argtypes = [C.c_void_p, C.c_int64, C.c_int, _dp, _dp, _dp, _fp, _bp]
+    L.nb_flush_l2.argtypes = [C.c_void_p]
+    L.nb_device_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4
+    L.nb_alloc_pinned.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    L.nb_free_pinned.argtypes = [C.c_void_p]
     L.nb_download.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_download3.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
@@ -142,6 +147,19 @@ def partition(n, rank, world):
     lo, hi = C.c_int64(), C.c_int64()
     _check(load_library().nb_partition(n, rank, world, C.byref(lo), C.byref(hi)))
     return lo.value, hi.value
+
+
+def pinned_array(shape, dtype):
+    """numpy array over page-locked host memory (nb_alloc_pinned); freed with the array."""
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    ptr = C.c_void_p()
+    _check(load_library().nb_alloc_pinned(nbytes, C.byref(ptr)))
+    buf = (C.c_char * max(nbytes, 1)).from_address(ptr.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    import weakref
+    weakref.finalize(buf, load_library().nb_free_pinned, ptr)
+    return arr
 
 
 def comm_unique_id():
@@ -211,6 +229,27 @@ class Physics:
         _check(fn(self._h, n, pos.ctypes.data_as(_dp), vel.ctypes.data_as(_dp), mass.ctypes.data_as(_fp),
                   None if pin is None else pin.ctypes.data_as(_bp)))
         self.dim = dim
+
+    def upload_state(self, pos, vel, acc, mass, pinned=None):
+        """upload() that also carries the caller's Acceleration components (asserted == a(x))."""
+        n, dim = pos.shape
+        _check(self._L.nb_upload_state(self._h, n, dim, pos.ctypes.data_as(_dp), vel.ctypes.data_as(_dp),
+                                       None if acc is None else acc.ctypes.data_as(_dp), mass.ctypes.data_as(_fp),
+                                       None if pinned is None else pinned.ctypes.data_as(_bp)))
+        self.dim = dim
+
+    def download_into(self, pos, vel, acc):
+        """download() into caller-owned (n,dim) float64 arrays (e.g. pinned ones)."""
+        fn = self._L.nb_download if self.dim == 2 else self._L.nb_download3
+        _check(fn(self._h, *[None if a is None else a.ctypes.data_as(_dp) for a in (pos, vel, acc)]))
+
+    def device_info(self):
+        v = [C.c_int() for _ in range(4)]
+        _check(self._L.nb_device_info(self._h, *[C.byref(x) for x in v]))
+        return dict(sm_count=v[0].value, cc=(v[1].value, v[2].value), sm_clock_khz=v[3].value)
+
+    def flush_l2(self):
+        _check(self._L.nb_flush_l2(self._h))
 
     def download(self, pos=True, vel=True, acc=True):
         """(pos, vel, acc) as (n,dim) float64; a sharded context fills its own rows only."""

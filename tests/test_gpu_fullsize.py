@@ -1,0 +1,57 @@
+"""BASELINE.json's full size (config 4: N = 2^20 Plummer sphere, Velocity Verlet) checked
+through size-independent properties, since the reference's O(N^2) FP64 loop needs ~1 h there:
+  * Newton's third law: sum_i m_i a_i = 0 up to FP32 pair rounding;
+  * a seeded subsample of targets against an FP64 direct sum over all 2^20 sources
+    (numpy restatement of the oracle's pair term), tolerance 1e-5 per body;
+  * energy conservation over fused Verlet steps from the fused potential."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+N = 1 << 20
+
+
+def direct_sum_fp64(pos, mass, targets, g, eps):
+    """a_t = sum_k G m_k (x_k - x_t) / (r^2 + eps^2)^1.5, FP64 (Physics.hpp:237-246 terms)."""
+    m = mass.astype(np.float64)
+    out = np.zeros((len(targets), pos.shape[1]))
+    for q, t in enumerate(targets):
+        d = pos - pos[t]
+        r2 = (d * d).sum(axis=1) + eps * eps
+        w = g * m / (r2 * np.sqrt(r2))
+        w[t] = 0.0
+        out[q] = (w[:, None] * d).sum(axis=0)
+    return out
+
+
+def test_c4_full_size_properties(pkg):
+    pos, vel, mass = pkg.scenarios.plummer(N, seed=1234, dim=3)
+    eps = 3.844e8 / np.sqrt(N)
+    ph = pkg.Physics(0)
+    ph.set_config(softening=eps)
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    _, _, acc = ph.download()
+    assert np.isfinite(acc).all()
+    m = mass.astype(np.float64)[:, None]
+    net = np.abs((m * acc).sum(axis=0)).max()
+    gross = np.abs(m * acc).sum()
+    assert net <= 1e-6 * gross, f"third-law residual {net / gross:.3e}"
+    rng = np.random.default_rng(7)
+    targets = np.concatenate([rng.integers(0, N, 60), [0, 1, 511, 512, N - 2, N - 1]])
+    ref = direct_sum_fp64(pos, mass, targets, 6.67430e-11, eps)
+    err = np.linalg.norm(acc[targets] - ref, axis=1) / np.linalg.norm(ref, axis=1)
+    assert err.max() <= 1e-5, f"subsample max rel err {err.max():.3e}"
+
+    dt = 1e-3 * pkg.scenarios.crossing_time(N)
+    ph.step(dt, 1, diagnostics=True)
+    d0 = ph.step_diagnostics()
+    ph.step(dt, 3, diagnostics=True)
+    d1 = ph.step_diagnostics()
+    assert d0.ok and d1.ok
+    assert abs((d1.energy - d0.energy) / d0.energy) < 1e-6
+    assert d0.total_mass == pytest.approx(float(mass.astype(np.float64).sum()), rel=1e-12)
+    c = ph.counters()
+    assert c["force_evals"] == 5 and c["interactions"] >= 5.0 * N * N
+    ph.close()

@@ -1,0 +1,408 @@
+"""Parity of the CUDA path (through the C-ABI) with the reference: against the committed
+fixtures the unmodified reference generated (tests/golden/) and against the oracle
+(oracle/nbody_oracle.c, itself pinned bit-for-bit to the reference by tests/test_oracle.py)
+on the same seeded inputs.
+
+Stated tolerances (BASELINE.json north_star):
+  * FP32 path: per-body |a - a_ref| / |a_ref| <= 1e-5 (max over bodies);
+  * FP64_EXACT path: bit-identical accelerations and trajectories;
+  * diagnostics: 1e-6 relative on energies for the FP32 potential, 1e-12 for FP64 sums;
+  * FP32 trajectory divergence max|x - x_ref| / R after K steps: bounds in each test.
+"""
+import numpy as np
+import pytest
+
+from conftest import golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+ACC_TOL = 1e-5
+
+
+@pytest.fixture()
+def ph(pkg):
+    p = pkg.Physics(0)
+    yield p
+    p.close()
+
+
+def zeros_like_state(pos):
+    return np.zeros_like(pos), np.zeros_like(pos)
+
+
+# ---- config 2: 4096-body uniform disk, accelerations ------------------------------------
+def test_c2_disk_accelerations_fp32(pkg, ph):
+    g = golden("c2_disk_4096.npz")
+    pos, mass = g["pos"], g["mass"]
+    ph.set_config(integrator=0)
+    ph.upload(pos, np.zeros_like(pos), mass)
+    ph.compute_gravity()
+    _, _, acc = ph.download()
+    e = rel_err(acc, g["acc"])
+    assert e.max() <= ACC_TOL, f"max rel err {e.max():.3e}"
+    assert np.quantile(e, 0.999) <= 5e-6 and np.median(e) <= 5e-7
+    # cancellation-normalised error: |da| / sum_j |term_j| is far below FP32 epsilon
+    assert ph.counters()["force_evals"] == 1
+
+
+def test_c2_disk_accelerations_exact_bitwise(pkg, ph):
+    g = golden("c2_disk_4096.npz")
+    ph.set_precision(pkg.PRECISION_FP64_EXACT)
+    ph.upload(g["pos"], np.zeros_like(g["pos"]), g["mass"])
+    ph.compute_gravity()
+    _, _, acc = ph.download()
+    assert np.array_equal(acc, g["acc"])
+
+
+def test_c2_euler_short_run_tracks_oracle(pkg, ph, oracle_lib, ob):
+    pos, vel, mass = pkg.scenarios.uniform_disk(4096, seed=1234, circular=True)
+    ph.set_config(integrator=0)
+    ph.upload(pos, vel, mass)
+    dt = 300.0
+    ph.step(dt, 20)
+    p, v, a = ph.download()
+    po, vo = pos.copy(), vel.copy()
+    ao, a0 = zeros_like_state(pos)
+    oracle_lib.physics_frames(po, vo, ao, a0, mass, np.zeros(4096, np.uint8), ob.make_config(integrator=0), dt, 20)
+    R = 3.844e8
+    assert np.abs(p - po).max() / R < 1e-9
+    assert np.abs(v - vo).max() / np.abs(vo).max() < 1e-6
+    assert rel_err(a, ao).max() <= ACC_TOL  # Acceleration holds a(x) of the last force pass
+
+
+# ---- config 1: three-body seed ----------------------------------------------------------------
+@pytest.mark.parametrize("integ,name", [(1, "verlet"), (0, "euler")])
+def test_c1_three_body_10k_steps_bitexact(pkg, ph, integ, name):
+    """AUTO precision picks the FP64 exact path for 3 bodies: the 10 000-step run is
+    bit-identical to the reference's (fixture written by the unmodified reference)."""
+    g = golden("c1_three_body.npz")
+    ph.set_config(integrator=integ)
+    ph.reset_scenario()
+    p, v, _ = ph.download()
+    assert np.array_equal(p, g["seed_pos"]) and np.array_equal(v, g["seed_vel"])
+    d0 = ph.compute_diagnostics()
+    assert d0.ok and np.allclose(d0.as_reference_array(), g[f"{name}_diag0"], rtol=1e-14, atol=0)
+    dt = float(g["dt_eff"])
+    done = 0
+    for upto in (100, 1000, 10000):
+        ph.step(dt, upto - done)
+        done = upto
+        p, v, a = ph.download()
+        assert np.array_equal(p, g[f"{name}_pos_{upto}"]), upto
+        assert np.array_equal(v, g[f"{name}_vel_{upto}"]), upto
+        assert np.array_equal(a, g[f"{name}_acc_{upto}"]), upto
+    d = ph.compute_diagnostics()
+    ref = g[f"{name}_diag_10000"]
+    assert np.allclose(d.as_reference_array()[:3], ref[:3], rtol=1e-13, atol=0)
+    assert d.momentum[0] == 0.0 and d.momentum[1] == 0.0 and np.array_equal(p[0], [0.0, 0.0])
+    # energy drift within the reference's own drift on the same scenario
+    drift = abs((d.energy - d0.energy) / d0.energy)
+    assert drift <= float(g[f"{name}_max_drift_10000"]) * (1 + 1e-9)
+
+
+@pytest.mark.parametrize("integ,name,tol_x,tol_e", [(1, "verlet", 2e-6, 2.0e-6), (0, "euler", 5e-6, 5.5e-4)])
+def test_c1_three_body_fp32_divergence_bound(pkg, ph, integ, name, tol_x, tol_e):
+    """The FP32 path on the same seed: bounded divergence over 1000 steps and the same energy
+    drift as the reference. (The mirror-symmetric seed is dynamically unstable: any rounding
+    difference grows e-fold per ~600 steps, so no FP32 evaluation can track 10k steps; DESIGN.md.)"""
+    g = golden("c1_three_body.npz")
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(integrator=integ)
+    ph.reset_scenario()
+    d0 = ph.compute_diagnostics()
+    dt = float(g["dt_eff"])
+    ph.step(dt, 100)
+    p, _, _ = ph.download()
+    assert np.abs(p - g[f"{name}_pos_100"]).max() / 3.844e8 < 1e-7
+    ph.step(dt, 900)
+    p, _, _ = ph.download()
+    assert np.abs(p - g[f"{name}_pos_1000"]).max() / 3.844e8 < tol_x
+    d = ph.compute_diagnostics()
+    assert abs((d.energy - d0.energy) / d0.energy) < tol_e
+
+
+# ---- filters, pins, speed cap, substeps ----------------------------------------------------------
+@pytest.mark.parametrize("integ,name", [(1, "verlet"), (0, "euler")])
+def test_mixed_bodies_exact_path_bitwise(pkg, ph, integ, name):
+    g = golden("mixed_256.npz")
+    ph.set_config(integrator=integ, max_substep=3000.0, max_speed=2000.0)
+    ph.upload(g["pos"], g["vel"], g["mass"], g["pinned"])
+    ph.compute_gravity()
+    _, _, a0 = ph.download()
+    assert np.array_equal(a0, g[f"{name}_acc0"])
+    ph.step(8333.333984375, 3)
+    p, v, a = ph.download()
+    assert np.array_equal(p, g[f"{name}_pos"], equal_nan=True)
+    assert np.array_equal(v, g[f"{name}_vel"], equal_nan=True)
+    assert np.array_equal(a, g[f"{name}_acc"], equal_nan=True)
+    d = ph.compute_diagnostics()
+    assert not d.ok and d.energy == 0.0  # non-finite bodies: zeroed struct, ok = false (Physics.hpp:140-145)
+
+
+@pytest.mark.parametrize("integ,name", [(1, "verlet"), (0, "euler")])
+def test_mixed_bodies_fp32_path(pkg, ph, integ, name):
+    """Same semantics on the FP32 fused path: filtered bodies keep stale accelerations and do not
+    attract, pinned bodies attract but never move, speed cap after the kick, 3 substeps per frame."""
+    g = golden("mixed_256.npz")
+    pinned = g["pinned"]
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(integrator=integ, max_substep=3000.0, max_speed=2000.0)
+    ph.upload(g["pos"], g["vel"], g["mass"], pinned)
+    ph.compute_gravity()
+    _, _, a0 = ph.download()
+    ref0 = g[f"{name}_acc0"]
+    moving = np.linalg.norm(ref0, axis=1) > 0
+    assert rel_err(a0[moving], ref0[moving]).max() <= ACC_TOL
+    assert not a0[~moving].any()  # pinned, m <= 0, non-finite: exactly zero
+    ph.step(8333.333984375, 3)
+    p, v, a = ph.download()
+    P, V = g[f"{name}_pos"], g[f"{name}_vel"]
+    fin = np.isfinite(P).all(axis=1) & np.isfinite(V).all(axis=1)
+    assert np.array_equal(np.isfinite(p).all(axis=1) & np.isfinite(v).all(axis=1), fin)
+    assert np.array_equal(p[pinned == 1], g["pos"][pinned == 1], equal_nan=True)
+    scale = np.abs(P[fin]).max()
+    assert np.abs(p[fin] - P[fin]).max() / scale < 1e-7
+    assert np.abs(v[fin] - V[fin]).max() / 2000.0 < 1e-5
+    speeds = np.linalg.norm(v[fin & (pinned == 0)], axis=1)
+    assert speeds.max() <= 2000.0 * (1 + 1e-12)
+
+
+def test_zero_net_momentum(pkg, ph):
+    g = golden("mixed_256.npz")
+    ph.upload(g["pos"], g["vel"], g["mass"], g["pinned"])
+    ph.zero_net_momentum()
+    _, v, _ = ph.download()
+    ref = g["zeroed_vel"]
+    # the reference's sums run over non-pinned bodies including the non-finite one: all NaN there
+    assert np.array_equal(np.isnan(v), np.isnan(ref))
+    # on clean input: tree-ordered FP64 sums vs the reference's sequential ones
+    pos, vel, mass = pkg.scenarios.plummer(4096, seed=3, dim=2)
+    pin = np.zeros(4096, np.uint8)
+    pin[::97] = 1
+    ph.upload(pos, vel, mass, pin)
+    ph.zero_net_momentum()
+    _, v, _ = ph.download()
+    from oracle import bindings as ob
+    vo = vel.copy()
+    ob.Oracle().zero_net_momentum(vo, mass, pin)
+    assert np.abs(v - vo).max() <= 1e-12 * np.abs(vo).max()
+    assert not v[pin == 1].any()
+
+
+# ---- diagnostics ------------------------------------------------------------------------------
+def test_diagnostics_match_reference_fixture(pkg, ph):
+    g = golden("plummer2d_1024.npz")
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.upload(g["pos"], g["vel"], g["mass"])
+    d = ph.compute_diagnostics()
+    ref = g["diag"]
+    assert d.ok
+    got = d.as_reference_array()
+    assert abs(got[0] - ref[0]) <= 1e-13 * abs(ref[0])      # KE: FP64 sums
+    assert abs(got[1] - ref[1]) <= 1e-6 * abs(ref[1])       # PE: FP32 pair terms, FP64 accumulation
+    assert abs(got[2] - ref[2]) <= 2e-6 * abs(ref[2])
+    pscale = np.abs(g["mass"].astype(np.float64)[:, None] * g["vel"]).sum()
+    assert np.abs(got[3:5] - ref[3:5]).max() <= 1e-13 * pscale
+    assert np.abs(got[5:7] - ref[5:7]).max() <= 1e-13 * np.abs(g["pos"]).max()
+    assert got[7] == pytest.approx(ref[7], rel=1e-14)
+    ph.set_precision(pkg.PRECISION_FP64_EXACT)
+    de = ph.compute_diagnostics().as_reference_array()
+    assert np.allclose(de[:3], ref[:3], rtol=1e-13, atol=0)
+
+
+def test_fused_step_diagnostics_equal_standalone(pkg, ph, oracle_lib, ob):
+    """nb_step_with_diagnostics: potential accumulated inside the force pass == a separate
+    compute_diagnostics of the end state == the oracle on the oracle's trajectory."""
+    n = 8192
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=11, dim=2)
+    dt = 2e-3 * pkg.scenarios.crossing_time(n)
+    ph.set_config(softening=1.0e6)
+    ph.upload(pos, vel, mass)
+    ph.step(dt, 3, diagnostics=True)
+    fused = ph.step_diagnostics()
+    alone = ph.compute_diagnostics()
+    assert fused.ok and alone.ok
+    assert abs(fused.kinetic - alone.kinetic) <= 1e-13 * abs(alone.kinetic)
+    assert abs(fused.potential - alone.potential) <= 1e-6 * abs(alone.potential)
+    po, vo = pos.copy(), vel.copy()
+    ao, a0 = zeros_like_state(pos)
+    oracle_lib.physics_frames(po, vo, ao, a0, mass, np.zeros(n, np.uint8), ob.make_config(softening=1.0e6), dt, 3)
+    ref, ok = oracle_lib.compute_diagnostics(po, vo, mass, softening=1.0e6)
+    assert ok and abs(fused.energy - ref[2]) <= 2e-6 * abs(ref[2])
+    assert abs(fused.kinetic - ref[0]) <= 1e-7 * abs(ref[0])
+
+
+def test_c3_plummer_65536_energy_momentum(pkg, ph, oracle_lib):
+    """Config 3: 65 536-body Plummer sphere (projected to the reference's 2-D), Verlet with
+    per-step diagnostics. E0 against the oracle's O(N^2) FP64 loop; drift and momentum bounds."""
+    n = 65536
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=1234, dim=2)
+    eps = 3.844e8 / np.sqrt(n)
+    ph.set_config(softening=eps)
+    ph.upload(pos, vel, mass)
+    ph.zero_net_momentum()
+    _, vz, _ = ph.download(pos=False, acc=False)
+    ref, ok = oracle_lib.compute_diagnostics(pos, vz, mass, softening=eps)
+    d0 = ph.compute_diagnostics()
+    assert ok and d0.ok
+    assert abs(d0.energy - ref[2]) <= 2e-6 * abs(ref[2])
+    assert abs(d0.potential - ref[1]) <= 1e-6 * abs(ref[1])
+    dt = 1e-3 * pkg.scenarios.crossing_time(n)
+    drift = 0.0
+    pscale = float(np.abs(mass.astype(np.float64)[:, None] * vz).sum())
+    for _ in range(10):
+        ph.step(dt, 1, diagnostics=True)
+        d = ph.step_diagnostics()
+        assert d.ok
+        drift = max(drift, abs((d.energy - d0.energy) / d0.energy))
+        assert np.abs(d.momentum).max() <= 1e-6 * pscale
+    assert drift < 1e-5
+
+
+# ---- 3-D state and the reference statics one by one ----------------------------------------------
+def test_3d_accelerations_and_steps_vs_oracle3(pkg, ph, oracle_lib, ob):
+    n = 4096
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=21, dim=3)
+    eps = 1.0e6
+    ph.set_config(softening=eps)
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    _, _, acc = ph.download()
+    ref = oracle_lib.compute_gravity(pos, vel, mass, softening=eps)
+    assert rel_err(acc, ref).max() <= ACC_TOL
+    dt = 1e-3 * pkg.scenarios.crossing_time(n)
+    ph.step(dt, 5)
+    p, v, _ = ph.download()
+    po, vo = pos.copy(), vel.copy()
+    ao, a0 = zeros_like_state(pos)
+    oracle_lib.physics_frames(po, vo, ao, a0, mass, np.zeros(n, np.uint8), ob.make_config(softening=eps), dt, 5)
+    assert np.abs(p - po).max() / 3.844e8 < 1e-9
+    d = ph.compute_diagnostics()
+    dr, ok = oracle_lib.compute_diagnostics(po, vo, mass, softening=eps)
+    assert ok and abs(d.energy - dr[2]) <= 2e-6 * abs(dr[2])
+    assert np.abs(d.com - dr[6:9]).max() <= 1e-9 * 3.844e8
+
+
+@pytest.mark.parametrize("integ", [0, 1])
+def test_compute_gravity_then_integrate_like_sys2_sys3(pkg, ph, oracle_lib, ob, integ):
+    """nb_compute_gravity + nb_integrate called separately (the un-fused drop-in) equal nb_step."""
+    n = 2048
+    pos, vel, mass = pkg.scenarios.uniform_disk(n, seed=5, circular=True)
+    cfgkw = dict(integrator=integ, max_substep=400.0)
+    dt = 1000.0
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(**cfgkw)
+    ph.upload(pos, vel, mass)
+    for _ in range(2):
+        ph.compute_gravity()
+        ph.integrate(dt)
+    p1, v1, a1 = ph.download()
+    ph.upload(pos, vel, mass)
+    ph.step(dt, 2)
+    p2, v2, a2 = ph.download()
+    assert np.array_equal(p1, p2) and np.array_equal(v1, v2)  # same kernels, same order: bitwise
+    po, vo = pos.copy(), vel.copy()
+    ao, a0 = zeros_like_state(pos)
+    oracle_lib.physics_frames(po, vo, ao, a0, mass, np.zeros(n, np.uint8), ob.make_config(**cfgkw), dt, 2)
+    assert pkg.substep_plan(dt, 400.0, 200)[0] == 3
+    assert np.abs(p1 - po).max() / 3.844e8 < 1e-9
+
+
+def test_bitwise_reproducible_and_split_independent(pkg):
+    """Fixed summation order: repeated runs are bit-identical; a different source split
+    (nseg) changes only the FP64 combination order (<= 1e-13 relative)."""
+    import os
+    n = 6000
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=8, dim=3)
+    runs = []
+    for nseg in ("0", "0", "3", "7"):
+        os.environ["NB_FORCE_NSEG"] = nseg
+        p = pkg.Physics(0)
+        p.upload(pos, vel, mass)
+        p.step(50.0, 3)
+        runs.append(p.download())
+        p.close()
+    os.environ.pop("NB_FORCE_NSEG")
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+    for other in runs[2:]:
+        assert np.abs(other[2] - runs[0][2]).max() <= 1e-12 * np.abs(runs[0][2]).max()
+
+
+def test_all_kernel_variants_agree(pkg):
+    import os
+    g = golden("c2_disk_4096.npz")
+    for packed in ("1", "0"):
+        for r in ("4", "2", "1"):
+            os.environ["NB_FORCE_R"], os.environ["NB_FORCE_PACKED"] = r, packed
+            p = pkg.Physics(0)
+            p.upload(g["pos"], np.zeros_like(g["pos"]), g["mass"])
+            p.compute_gravity()
+            acc = p.download()[2]
+            p.close()
+            assert rel_err(acc, g["acc"]).max() <= ACC_TOL, (packed, r)
+    os.environ.pop("NB_FORCE_R")
+    os.environ.pop("NB_FORCE_PACKED")
+
+
+# ---- edge cases -------------------------------------------------------------------------------
+def test_empty_single_and_ragged_worlds(pkg, ph, oracle_lib):
+    e2, e1 = np.zeros((0, 2)), np.zeros(0, np.float32)
+    ph.upload(e2, e2, e1)
+    ph.compute_gravity()
+    ph.step(1.0, 3)
+    d = ph.compute_diagnostics()
+    assert d.ok and d.energy == 0.0 and ph.num_bodies() == 0
+    ph.upload(np.array([[1.0, 2.0]]), np.array([[3.0, 4.0]]), np.array([5.0], np.float32))
+    ph.step(2.0, 1)
+    p, v, a = ph.download()
+    assert np.array_equal(p, [[7.0, 10.0]]) and np.array_equal(v, [[3.0, 4.0]]) and not a.any()
+    ph.set_precision(pkg.PRECISION_FP32)
+    for n in (2, 511, 513, 1023, 1537):  # tile tails, odd pair tails
+        pos, vel, mass = pkg.scenarios.uniform_disk(n, seed=n)
+        ph.upload(pos, vel, mass)
+        ph.compute_gravity()
+        acc = ph.download()[2]
+        ref = oracle_lib.compute_gravity(pos, vel, mass)
+        assert rel_err(acc, ref).max() <= ACC_TOL, n
+
+
+def test_zero_softening_and_coincident_bodies(pkg, ph, oracle_lib):
+    """eps = 0 is allowed (Constants.hpp:64): the full N x N sweep must not produce NaN from
+    the self term."""
+    n = 1000
+    pos, vel, mass = pkg.scenarios.uniform_disk(n, seed=77)
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(softening=0.0)
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    acc = ph.download()[2]
+    ref = oracle_lib.compute_gravity(pos, vel, mass, softening=0.0)
+    assert np.isfinite(acc).all() and rel_err(acc, ref).max() <= ACC_TOL
+
+
+def test_errors_are_status_codes(pkg, ph):
+    with pytest.raises(pkg.NbodyError) as e:
+        ph.set_config(integrator=7)
+    assert e.value.status == 1
+    with pytest.raises(pkg.NbodyError):
+        ph.upload(np.zeros((4, 5)), np.zeros((4, 5)), np.zeros(4, np.float32))
+    with pytest.raises(pkg.NbodyError):
+        ph.set_precision(9)
+
+
+def test_far_escaper_rescales_packed_units(pkg, ph, oracle_lib, ob):
+    """A body that runs away grows the extent by orders of magnitude between steps; the
+    power-of-two length unit follows it (rotating extent slots) and forces stay in tolerance."""
+    n = 1024
+    pos, vel, mass = pkg.scenarios.uniform_disk(n, seed=4)
+    vel[0] = [3.0e9, 0.0]  # crosses ~8 system radii per step
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(integrator=0)
+    ph.upload(pos, vel, mass)
+    ph.step(1.0, 12)
+    ph.compute_gravity()
+    p, v, a = ph.download()
+    ref = oracle_lib.compute_gravity(p, v, mass)
+    assert np.isfinite(a).all() and rel_err(a[1:], ref[1:]).max() <= ACC_TOL
+    assert p[0, 0] > 3.0e10

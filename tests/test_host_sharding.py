@@ -1,0 +1,54 @@
+"""World-size-2 CPU tests (gloo) of the host-side plumbing of target-partitioned runs:
+id broadcast, partition agreement across ranks, assembly of per-rank row slices and the
+max-over-ranks timing reduction. The per-step NCCL exchange itself is covered by the -m gpu
+tests / bench at N > 1."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, n, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # rank 0 draws the id; everyone must end up with the same 128 bytes
+        uid = pkg.sharded.broadcast_unique_id(dist, make_id=lambda: bytes(range(128)))
+        assert uid == bytes(range(128))
+        lo, hi = pkg.partition(n, rank, world)
+        full = np.arange(n * 2, dtype=np.float64).reshape(n, 2)
+        mine = np.zeros_like(full)
+        mine[lo:hi] = full[lo:hi]          # what Physics.download returns on a sharded context
+        got = pkg.sharded.gather_rows(dist, mine, n)
+        assert np.array_equal(got, full)
+        assert pkg.sharded.max_over_ranks(dist, 10.0 + rank) == 10.0 + world - 1
+        assert pkg.sharded.sum_over_ranks(dist, hi - lo) == n
+        np.save(os.path.join(out_dir, f"ok{rank}.npy"), np.array([lo, hi]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [3, 1000, 4096 + 5])
+def test_two_rank_gloo_plumbing(pkg, tmp_path, n):
+    import torch.multiprocessing as mp
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, n, str(tmp_path)), nprocs=2, join=True)
+    spans = [np.load(tmp_path / f"ok{r}.npy") for r in range(2)]
+    assert spans[0][0] == 0 and spans[0][1] == spans[1][0] and spans[1][1] == n
