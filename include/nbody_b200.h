@@ -54,7 +54,7 @@ typedef struct nb_config {
 } nb_config;
 
 /* Arithmetic of the force evaluation (nb_set_precision).
- *   FP32       the hot path: FP32 pair terms, FP64 accumulation across 32-source chunks and
+ *   FP32       the hot path: FP32 pair terms, FP64 accumulation across 64-source chunks and
  *              FP64 integrator state; per-body acceleration within 1e-5 of the reference.
  *   FP64_EXACT the reference's own FP64 operation order (Physics.hpp:237-254), bit-identical
  *              accelerations and trajectories; about 1/15 of the FP32 throughput.

@@ -19,7 +19,7 @@ namespace nb {
 
 constexpr int kTileBodies = 512;          // j-bodies per shared-memory stage (16 KB)
 constexpr int kStages = 2;                // TMA bulk-copy ring depth
-constexpr int kFlushChunk = 32;           // FP32 partial sums are folded into FP64 every 32 sources
+constexpr int kFlushChunk = 64;           // FP32 partial sums are folded into FP64 every 64 sources
 constexpr int kExtentSlots = 4;           // rotating max|x| slots, see scale_for()
 constexpr int kHeadroomLog2 = 17;         // scaled |x| < 2^17 when packed; r^6 stays finite up to 2^19
 constexpr int kMaxSegments = 16;          // j-split factor upper bound

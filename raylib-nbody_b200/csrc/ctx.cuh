@@ -80,7 +80,7 @@ struct nb_ctx {
 
     // ---- launch plans ----
     nb::LaunchPlan plans[3][2];  // [all | own sources | remote sources][without / with potential]
-    int forced_r = 0, forced_packed = -1, forced_nseg = 0;
+    int forced_r = 0, forced_packed = -1, forced_nseg = 0, forced_chunk = nb::kFlushChunk, forced_minb = 4;
 
     // ---- measurement ----
     long long kernel_launches = 0;

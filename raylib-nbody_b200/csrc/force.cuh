@@ -93,16 +93,16 @@ struct Target<true, POT> {
     }
 };
 
-// One flush chunk (kFlushChunk sources = kFlushChunk/2 pair records) against R targets.
+// One flush chunk (CH sources = CH/2 pair records) against R targets.
 // MASK: the chunk may contain one of this CTA's own targets; its mass is zeroed for that
 // target so the potential carries no self term (the force self term is exactly 0 anyway).
-template <int R, bool PACKED, bool POT, bool MASK>
+template <int R, bool PACKED, bool POT, bool MASK, int CH>
 __device__ __forceinline__ void chunk_interact(Target<PACKED, POT> (&t)[R], const float4* __restrict__ rec,
                                                float eps2, long long j_first, const long long (&ti)[R]) {
     if constexpr (PACKED) {
         const f2 e2 = f2_make(eps2, eps2);
 #pragma unroll
-        for (int u = 0; u < kFlushChunk / 2; ++u) {
+        for (int u = 0; u < CH / 2; ++u) {
             const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(rec + 2 * u);
             const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(rec + 2 * u + 1);
             f2 xj{A.x}, yj{A.y}, zj{B.x}, mj{B.y};
@@ -120,7 +120,7 @@ __device__ __forceinline__ void chunk_interact(Target<PACKED, POT> (&t)[R], cons
         }
     } else {
 #pragma unroll
-        for (int u = 0; u < kFlushChunk / 2; ++u) {
+        for (int u = 0; u < CH / 2; ++u) {
             const float4 A = rec[2 * u];
             const float4 B = rec[2 * u + 1];
 #pragma unroll

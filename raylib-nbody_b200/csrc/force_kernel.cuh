@@ -22,7 +22,7 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <int NT, int R, bool PACKED, bool POT, int MINB>
+template <int NT, int R, bool PACKED, bool POT, int MINB, int CH = kFlushChunk>
 __global__ void __launch_bounds__(NT, MINB)
 force_kernel(const __grid_constant__ StepParams p) {
     constexpr int IT = NT * R;
@@ -88,13 +88,13 @@ force_kernel(const __grid_constant__ StepParams p) {
         const long long j_tile = phys(t) * kTileBodies;
         const bool diag_tile = POT && (j_tile < i0 + IT) && (j_tile + kTileBodies > i0);
 #pragma unroll 1
-        for (int c = 0; c < kTileBodies / kFlushChunk; ++c) {
-            const float4* rec = &ring[s][c * kFlushChunk];
-            const long long j_first = j_tile + c * kFlushChunk;
+        for (int c = 0; c < kTileBodies / CH; ++c) {
+            const float4* rec = &ring[s][c * CH];
+            const long long j_first = j_tile + c * CH;
             if (diag_tile)
-                chunk_interact<R, PACKED, POT, true>(tg, rec, cur.eps2, j_first, ti);
+                chunk_interact<R, PACKED, POT, true, CH>(tg, rec, cur.eps2, j_first, ti);
             else
-                chunk_interact<R, PACKED, POT, false>(tg, rec, cur.eps2, j_first, ti);
+                chunk_interact<R, PACKED, POT, false, CH>(tg, rec, cur.eps2, j_first, ti);
 #pragma unroll
             for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
         }

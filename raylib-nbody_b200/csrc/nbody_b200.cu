@@ -118,22 +118,27 @@ constexpr int kNT = 128;
 typedef void (*ForceFn)(const StepParams);
 
 struct KernelEntry {
-    int r, packed, pot;
+    int r, packed, pot, chunk, minb;
     ForceFn fn;
 };
 
+#define NB_K(R, P, POT, MINB, CH) {R, P, POT, CH, MINB, force_kernel<kNT, R, (P) != 0, (POT) != 0, MINB, CH>}
 const KernelEntry kKernels[] = {
-    {4, 1, 0, force_kernel<kNT, 4, true, false, 4>},  {2, 1, 0, force_kernel<kNT, 2, true, false, 4>},
-    {1, 1, 0, force_kernel<kNT, 1, true, false, 4>},  {4, 0, 0, force_kernel<kNT, 4, false, false, 4>},
-    {2, 0, 0, force_kernel<kNT, 2, false, false, 4>}, {1, 0, 0, force_kernel<kNT, 1, false, false, 4>},
-    {2, 1, 1, force_kernel<kNT, 2, true, true, 4>},   {1, 1, 1, force_kernel<kNT, 1, true, true, 4>},
-    {2, 0, 1, force_kernel<kNT, 2, false, true, 4>},  {1, 0, 1, force_kernel<kNT, 1, false, true, 4>},
+    // production set: flush chunk kFlushChunk (64), 4 CTAs/SM
+    NB_K(4, 1, 0, 4, 64), NB_K(2, 1, 0, 4, 64), NB_K(1, 1, 0, 4, 64),
+    NB_K(4, 0, 0, 4, 64), NB_K(2, 0, 0, 4, 64), NB_K(1, 0, 0, 4, 64),
+    NB_K(2, 1, 1, 4, 64), NB_K(1, 1, 1, 4, 64), NB_K(2, 0, 1, 4, 64), NB_K(1, 0, 1, 4, 64),
+    // tuning set (NB_FORCE_CHUNK / NB_FORCE_MINB)
+    NB_K(4, 1, 0, 4, 32), NB_K(2, 1, 0, 6, 64), NB_K(4, 1, 0, 3, 64),
 };
+#undef NB_K
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
 
-const KernelEntry* find_kernel(int r, int packed, int pot) {
+const KernelEntry* find_kernel(int r, int packed, int pot, int chunk = kFlushChunk, int minb = 4) {
     for (int k = 0; k < kNumKernels; ++k)
-        if (kKernels[k].r == r && kKernels[k].packed == packed && kKernels[k].pot == pot) return &kKernels[k];
+        if (kKernels[k].r == r && kKernels[k].packed == packed && kKernels[k].pot == pot && kKernels[k].chunk == chunk &&
+            kKernels[k].minb == minb)
+            return &kKernels[k];
     return nullptr;
 }
 
@@ -149,7 +154,7 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
     for (int q = 0; q < n_opts; ++q) {
         const int r = r_opts[q];
         if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 2 && r == 2)) continue;
-        const KernelEntry* ke = find_kernel(r, packed, pot ? 1 : 0);
+        const KernelEntry* ke = pot ? find_kernel(r, packed, 1) : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb);
         if (!ke) continue;
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
@@ -350,6 +355,8 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
     if (const char* v = getenv("NB_FORCE_PACKED")) c->forced_packed = atoi(v);
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
+    if (const char* v = getenv("NB_FORCE_CHUNK")) c->forced_chunk = atoi(v);
+    if (const char* v = getenv("NB_FORCE_MINB")) c->forced_minb = atoi(v);
     *out = c;
     return NB_OK;
 }

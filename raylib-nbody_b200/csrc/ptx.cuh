@@ -50,6 +50,9 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
 }
 
 __device__ __forceinline__ float rsqrt_fast(float x) {
+#ifdef NB_UBENCH_NO_MUFU  // tools/ubench only: what-if without the SFU op (wrong numerics)
+    return __int_as_float(0x5f3759df - (__float_as_int(x) >> 1));
+#endif
     float y;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
