@@ -130,6 +130,7 @@ const KernelEntry kKernels[] = {
     NB_K(2, 1, 1, 4, 64), NB_K(1, 1, 1, 4, 64), NB_K(2, 0, 1, 4, 64), NB_K(1, 0, 1, 4, 64),
     // tuning set (NB_FORCE_CHUNK / NB_FORCE_MINB)
     NB_K(4, 1, 0, 4, 32), NB_K(2, 1, 0, 6, 64), NB_K(4, 1, 0, 3, 64),
+    NB_K(4, 1, 0, 5, 64), NB_K(3, 1, 0, 5, 64), NB_K(3, 1, 0, 6, 64), NB_K(2, 1, 0, 8, 64), NB_K(3, 1, 0, 4, 64),
 };
 #undef NB_K
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
@@ -147,10 +148,10 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
     LaunchPlan best;
     double best_score = -1.0;
     const int packed = c->forced_packed >= 0 ? c->forced_packed : 1;
-    const int r_opts_force[] = {4, 2, 1};
+    const int r_opts_force[] = {4, 3, 2, 1};
     const int r_opts_pot[] = {2, 1};
     const int* r_opts = pot ? r_opts_pot : r_opts_force;
-    const int n_opts = pot ? 2 : 3;
+    const int n_opts = pot ? 2 : 4;
     for (int q = 0; q < n_opts; ++q) {
         const int r = r_opts[q];
         if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 2 && r == 2)) continue;
@@ -168,7 +169,7 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
             const long long waves = (units + slots - 1) / slots;
             double eff = (double)units / (double)(waves * slots);
             // larger R amortises shared-memory reads; each extra segment costs a partial round-trip
-            const double score = eff * (r == 4 ? 1.0 : (r == 2 ? 0.97 : 0.90)) * (1.0 - 0.002 * (nseg - 1));
+            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.002 * (nseg - 1));
             if (score > best_score) {
                 best_score = score;
                 best.variant = (int)(ke - kKernels);

@@ -61,3 +61,18 @@ def golden(name):
 
 def rel_err(a, ref):
     return np.linalg.norm(a - ref, axis=1) / np.linalg.norm(ref, axis=1)
+
+
+def conditioning(pos, mass, eps=4.0):
+    """Per-body condition number of the direct sum: sum_j |term_ij| / |sum_j term_ij| (FP64, numpy).
+    A body whose pulls nearly cancel has a large value; any FP32 evaluation of the terms carries a
+    relative error of about (per-term rounding ~1e-7) x this number."""
+    n = len(pos)
+    out = np.empty(n)
+    m = mass.astype(np.float64)
+    for i in range(n):
+        d = pos - pos[i]
+        r2 = (d * d).sum(axis=1) + eps * eps
+        t = (m / (r2 * np.sqrt(r2)))[:, None] * d
+        out[i] = np.abs(t).sum() / max(np.linalg.norm(t.sum(axis=0)), 1e-300)
+    return out

@@ -6,7 +6,7 @@ import __graft_entry__ as ge
 pkg = ge.load_package(); sc = pkg.scenarios
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 18
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
-variants = [tuple(int(x) for x in v.split(",")) for v in sys.argv[3:]] or [(4,32,4),(4,64,4),(4,128,4),(2,32,5),(2,32,6),(2,64,5),(2,64,6),(2,64,4),(1,64,8),(4,64,3)]
+variants = [tuple(int(x) for x in v.split(",")) for v in sys.argv[3:]] or [(4,64,4),(4,64,5),(3,64,4),(3,64,5),(3,64,6),(2,64,6),(2,64,8),(4,64,3)]
 pos, vel, mass = sc.plummer(n, dim=3); dt = 1e-3 * sc.crossing_time(n); eps = 3.844e8 / np.sqrt(n)
 for r, ch, mb in variants:
     os.environ.update(NB_FORCE_R=str(r), NB_FORCE_CHUNK=str(ch), NB_FORCE_MINB=str(mb))
