@@ -17,12 +17,19 @@
 
 namespace nb {
 
-constexpr int kTileBodies = 512;          // j-bodies per shared-memory stage (16 KB)
-constexpr int kStages = 2;                // TMA bulk-copy ring depth
+constexpr int kTileBodies = 512;          // j-bodies per shared-memory stage (8 KB)
+#ifndef NB_STAGES
+#define NB_STAGES 2
+#endif
+#ifndef NB_RING_SYNC
+#define NB_RING_SYNC 1  // 1: hand stages back with a CTA-wide barrier instead of per-warp `empty` mbarriers
+#endif
+constexpr int kStages = NB_STAGES;         // TMA bulk-copy ring depth (8 KB stages)
 constexpr int kFlushChunk = 64;           // FP32 partial sums are folded into FP64 every 64 sources
 constexpr int kExtentSlots = 4;           // rotating max|x| slots, see scale_for()
 constexpr int kHeadroomLog2 = 17;         // scaled |x| < 2^17 when packed; r^6 stays finite up to 2^19
 constexpr int kMaxSegments = 16;          // j-split factor upper bound
+constexpr float kFarPacked = 1152921504606846976.0f;  // 2^60: packed x of non-attracting rows
 constexpr int kDiagValues = 12;           // KE, PE, Px,Py,Pz, Cx,Cy,Cz, M, nonfinite, pad, pad
 
 // Power-of-two scales for one generation of the j-stream.
@@ -104,6 +111,7 @@ struct StepParams {
     double g;
     double dt;                  // (double)dtSub
     double half_dt2;            // 0.5 * dt * dt, Physics.hpp:300
+    double eqm_mass;            // uniform-mass kernels: the common packed mass (1.0 otherwise)
 };
 
 }  // namespace nb

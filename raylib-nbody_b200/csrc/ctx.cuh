@@ -73,6 +73,10 @@ struct nb_ctx {
 
     int gen = 0;               // generation of pk[gen & 1]
     int mass_exp = 0;          // masses are packed as m * 2^-mass_exp
+    bool uniform_mass = false; // every body that can attract has the same mass -> no m*w multiply in the kernel
+    double uniform_packed_mass = 1.0;
+    bool planar = false;       // 2-D upload: z == 0 forever -> kernels skip the z terms
+    bool force_generic = false;
     bool acc_valid = false;    // Acceleration == a(x) for the current positions
     bool packed_valid = false; // pk[gen & 1] matches the current positions
     bool step_diag_valid = false;

@@ -35,7 +35,10 @@ __device__ __forceinline__ void cap_speed(double (&v)[3], float max_speed) {
 __device__ __forceinline__ void pack_body(float* __restrict__ pk, long long i, const double (&x)[3], float m,
                                           bool live, double inv_len, double inv_mass) {
     float* rec = pk + (i >> 1) * 8 + (i & 1);
-    rec[0] = live ? (float)__dmul_rn(x[0], inv_len) : 0.f;
+    // bodies dropped by the gather filter (and padding rows) sit at x = 2^60 packed units with m = 0:
+    // r^6 overflows to +inf, rsqrt(+inf) = +0, so they contribute exactly 0 even to the kernels
+    // that do not multiply by the mass (uniform-mass variant)
+    rec[0] = live ? (float)__dmul_rn(x[0], inv_len) : kFarPacked;
     rec[2] = live ? (float)__dmul_rn(x[1], inv_len) : 0.f;
     rec[4] = live ? (float)__dmul_rn(x[2], inv_len) : 0.f;
     rec[6] = live ? (float)__dmul_rn((double)m, inv_mass) : 0.f;

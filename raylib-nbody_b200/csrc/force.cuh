@@ -16,15 +16,23 @@
 #include "common.cuh"
 #include "ptx.cuh"
 
+#ifndef NB_UNROLL_PAIRS
+#define NB_UNROLL_PAIRS 32  // pair records per unrolled loop body (32 = a whole 64-source flush chunk)
+#endif
+
 namespace nb {
 
+constexpr int kUnrollPairs = NB_UNROLL_PAIRS;
+
 // One target body's running sums: FP32 inside a flush chunk, FP64 across chunks.
-template <bool PACKED, bool POT>
+// EQM: all sources carry the same mass -> the m*w multiply is dropped (the common factor is
+// applied in FP64 in the epilogue); D2: z == 0 for every body (reference 2-D uploads).
+template <bool PACKED, bool POT, bool EQM = false, bool D2 = false>
 struct Target;
 
 // ---- scalar FP32 variant ------------------------------------------------------------
 template <bool POT>
-struct Target<false, POT> {
+struct Target<false, POT, false, false> {
     float xi, yi, zi;
     float ax, ay, az, ph;
     __device__ __forceinline__ void init(float x, float y, float z) {
@@ -57,8 +65,8 @@ struct Target<false, POT> {
 };
 
 // ---- packed f32x2 variant (two sources per instruction) -------------------------------
-template <bool POT>
-struct Target<true, POT> {
+template <bool POT, bool EQM, bool D2>
+struct Target<true, POT, EQM, D2> {
     f2 nxi, nyi, nzi;  // {-x,-x} ... so dx = xj + (-xi) is one FADD2
     f2 ax, ay, az, ph;
     __device__ __forceinline__ void init(float x, float y, float z) {
@@ -66,18 +74,22 @@ struct Target<true, POT> {
         ax = ay = az = ph = f2_make(0.f, 0.f);
     }
     __device__ __forceinline__ void interact(f2 xj, f2 yj, f2 zj, f2 mj, f2 eps2) {
-        const f2 dx = f2_add(xj, nxi), dy = f2_add(yj, nyi), dz = f2_add(zj, nzi);
+        const f2 dx = f2_add(xj, nxi), dy = f2_add(yj, nyi);
         f2 r2 = f2_fma(dx, dx, eps2);
         r2 = f2_fma(dy, dy, r2);
-        r2 = f2_fma(dz, dz, r2);
+        f2 dz;
+        if (!D2) {
+            dz = f2_add(zj, nzi);
+            r2 = f2_fma(dz, dz, r2);
+        }
         const f2 r6 = f2_mul(f2_mul(r2, r2), r2);
         float lo, hi;
         f2_split(r6, lo, hi);
         const f2 w = f2_make(rsqrt_fast(lo), rsqrt_fast(hi));
-        const f2 s = f2_mul(mj, w);
+        const f2 s = EQM ? w : f2_mul(mj, w);
         ax = f2_fma(s, dx, ax);
         ay = f2_fma(s, dy, ay);
-        az = f2_fma(s, dz, az);
+        if (!D2) az = f2_fma(s, dz, az);
         if (POT) ph = f2_fma(mj, f2_mul(w, r2), ph);
     }
     // The even/odd-source halves are added in FP32 first: one commutative, sign-symmetric
@@ -87,7 +99,7 @@ struct Target<true, POT> {
         float lo, hi;
         f2_split(ax, lo, hi); Ax += (double)(lo + hi);
         f2_split(ay, lo, hi); Ay += (double)(lo + hi);
-        f2_split(az, lo, hi); Az += (double)(lo + hi);
+        if (!D2) { f2_split(az, lo, hi); Az += (double)(lo + hi); }
         ax = ay = az = f2_make(0.f, 0.f);
         if (POT) { f2_split(ph, lo, hi); Ph += (double)(lo + hi); ph = f2_make(0.f, 0.f); }
     }
@@ -96,16 +108,26 @@ struct Target<true, POT> {
 // One flush chunk (CH sources = CH/2 pair records) against R targets.
 // MASK: the chunk may contain one of this CTA's own targets; its mass is zeroed for that
 // target so the potential carries no self term (the force self term is exactly 0 anyway).
-template <int R, bool PACKED, bool POT, bool MASK, int CH>
-__device__ __forceinline__ void chunk_interact(Target<PACKED, POT> (&t)[R], const float4* __restrict__ rec,
+template <int R, bool PACKED, bool POT, bool MASK, int CH, bool EQM = false, bool D2 = false>
+__device__ __forceinline__ void chunk_interact(Target<PACKED, POT, EQM, D2> (&t)[R], const float4* __restrict__ rec,
                                                float eps2, long long j_first, const long long (&ti)[R]) {
     if constexpr (PACKED) {
         const f2 e2 = f2_make(eps2, eps2);
-#pragma unroll
+#pragma unroll kUnrollPairs
         for (int u = 0; u < CH / 2; ++u) {
             const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(rec + 2 * u);
-            const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(rec + 2 * u + 1);
-            f2 xj{A.x}, yj{A.y}, zj{B.x}, mj{B.y};
+            f2 xj{A.x}, yj{A.y}, zj{0ull}, mj{0ull};
+            constexpr bool kNeedM = !EQM || POT;
+            const unsigned long long* B64 = reinterpret_cast<const unsigned long long*>(rec + 2 * u + 1);
+            if (!D2 && kNeedM) {
+                const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(rec + 2 * u + 1);
+                zj.r = B.x;
+                mj.r = B.y;
+            } else if (!D2) {
+                zj.r = B64[0];
+            } else if (kNeedM) {
+                mj.r = B64[1];
+            }
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 f2 m = mj;

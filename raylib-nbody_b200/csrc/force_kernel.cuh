@@ -9,7 +9,8 @@
 //
 // The j-stream reaches shared memory through a kStages-deep ring of 1-D TMA bulk copies
 // (cp.async.bulk + mbarrier complete_tx): one elected thread issues 8 KB copies, nobody
-// spends issue slots on loads, and every warp reads sources with broadcast LDS.128.
+// spends issue slots on loads, and every warp reads sources with broadcast LDS.128. Stages are
+// handed back through `empty` mbarriers (one arrival per warp), not a CTA-wide barrier.
 #pragma once
 #include "epilogue.cuh"
 #include "force.cuh"
@@ -22,7 +23,7 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <int NT, int R, bool PACKED, bool POT, int MINB, int CH = kFlushChunk>
+template <int NT, int R, bool PACKED, bool POT, int MINB, int CH = kFlushChunk, bool EQM = false, bool D2 = false>
 __global__ void __launch_bounds__(NT, MINB)
 force_kernel(const __grid_constant__ StepParams p) {
     constexpr int IT = NT * R;
@@ -32,6 +33,7 @@ force_kernel(const __grid_constant__ StepParams p) {
 
     __shared__ alignas(128) float4 ring[kStages][kRecPerTile];
     __shared__ alignas(8) uint64_t full_bar[kStages];
+    __shared__ alignas(8) uint64_t empty_bar[kStages];
     __shared__ double red[kWarps][kDiagValues];
     __shared__ float red_ext[kWarps];
     __shared__ int is_last;
@@ -43,10 +45,11 @@ force_kernel(const __grid_constant__ StepParams p) {
     const long long i0 = p.i_lo + it * IT;
 
     // scales of the generation being read and of the one the epilogue packs (common.cuh)
-    const Scale cur = scale_for(p.extent[(p.gen + kExtentSlots - 1) % kExtentSlots], p.mass_exp, p.g, p.softening);
+    Scale cur = scale_for(p.extent[(p.gen + kExtentSlots - 1) % kExtentSlots], p.mass_exp, p.g, p.softening);
+    cur.acc_unit *= p.eqm_mass;
 
     // ---- targets ---------------------------------------------------------------------
-    Target<PACKED, POT> tg[R];
+    Target<PACKED, POT, EQM, D2> tg[R];
     long long ti[R];
     double S[R][4];
 #pragma unroll
@@ -67,7 +70,10 @@ force_kernel(const __grid_constant__ StepParams p) {
 
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < kStages; ++s) mbar_init(&full_bar[s], 1);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kWarps);
+        }
         fence_mbar_init();
     }
     __syncthreads();
@@ -81,6 +87,9 @@ force_kernel(const __grid_constant__ StepParams p) {
         }
     }
 
+    // No CTA-wide barrier in the tile loop: each warp releases a stage through its `empty`
+    // mbarrier, and the producer thread refills the stage released one tile earlier, so it only
+    // ever waits for a warp that has fallen a whole tile behind.
     for (long long t = t_begin; t < t_end; ++t) {
         const int k = (int)(t - t_begin);
         const int s = k % kStages;
@@ -92,17 +101,28 @@ force_kernel(const __grid_constant__ StepParams p) {
             const float4* rec = &ring[s][c * CH];
             const long long j_first = j_tile + c * CH;
             if (diag_tile)
-                chunk_interact<R, PACKED, POT, true, CH>(tg, rec, cur.eps2, j_first, ti);
+                chunk_interact<R, PACKED, POT, true, CH, EQM, D2>(tg, rec, cur.eps2, j_first, ti);
             else
-                chunk_interact<R, PACKED, POT, false, CH>(tg, rec, cur.eps2, j_first, ti);
+                chunk_interact<R, PACKED, POT, false, CH, EQM, D2>(tg, rec, cur.eps2, j_first, ti);
 #pragma unroll
             for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
         }
+#if NB_RING_SYNC
         __syncthreads();  // every warp is done with stage s
         if (tid == 0 && t + kStages < t_end) {
             mbar_arrive_expect_tx(&full_bar[s], kTileBytes);
             tma_load_1d(&ring[s][0], p.pk_cur + phys(t + kStages) * (kTileBodies * 4), kTileBytes, &full_bar[s]);
         }
+#else
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]);
+        if (tid == 0 && k >= 1 && t - 1 + kStages < t_end) {
+            const int sp = (k - 1) % kStages;
+            mbar_wait(&empty_bar[sp], (uint32_t)(((k - 1) / kStages) & 1));
+            mbar_arrive_expect_tx(&full_bar[sp], kTileBytes);
+            tma_load_1d(&ring[sp][0], p.pk_cur + phys(t - 1 + kStages) * (kTileBodies * 4), kTileBytes, &full_bar[sp]);
+        }
+#endif
     }
 
     // ---- combine source segments (fixed order) ------------------------------------------

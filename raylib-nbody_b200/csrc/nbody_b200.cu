@@ -114,31 +114,41 @@ int nccl_fail(int rc, const char* what) {
 // ---------------------------------------------------------------------------------------
 // force-kernel table and launch planning
 // ---------------------------------------------------------------------------------------
-constexpr int kNT = 128;
+#ifndef NB_NT
+#define NB_NT 128
+#endif
+constexpr int kNT = NB_NT;  // threads per CTA (developer A/B: -DNB_NT=256)
+constexpr int kCtaScale = kNT / 128;
 typedef void (*ForceFn)(const StepParams);
 
 struct KernelEntry {
-    int r, packed, pot, chunk, minb;
+    int r, packed, pot, chunk, minb, eqm, d2;
     ForceFn fn;
 };
 
-#define NB_K(R, P, POT, MINB, CH) {R, P, POT, CH, MINB, force_kernel<kNT, R, (P) != 0, (POT) != 0, MINB, CH>}
+#define NB_K(R, P, POT, MINB, CH) {R, P, POT, CH, MINB, 0, 0, force_kernel<kNT, R, (P) != 0, (POT) != 0, (MINB) / kCtaScale, CH>}
+// specialised packed force-only kernels: E uniform mass (no m*w multiply), D z == 0 (reference 2-D uploads)
+#define NB_KS(R, E, D) {R, 1, 0, 64, 4, E, D, force_kernel<kNT, R, true, false, 4 / kCtaScale, 64, (E) != 0, (D) != 0>}
 const KernelEntry kKernels[] = {
     // production set: flush chunk kFlushChunk (64), 4 CTAs/SM
     NB_K(4, 1, 0, 4, 64), NB_K(2, 1, 0, 4, 64), NB_K(1, 1, 0, 4, 64),
     NB_K(4, 0, 0, 4, 64), NB_K(2, 0, 0, 4, 64), NB_K(1, 0, 0, 4, 64),
     NB_K(2, 1, 1, 4, 64), NB_K(1, 1, 1, 4, 64), NB_K(2, 0, 1, 4, 64), NB_K(1, 0, 1, 4, 64),
-    // tuning set (NB_FORCE_CHUNK / NB_FORCE_MINB)
-    NB_K(4, 1, 0, 4, 32), NB_K(2, 1, 0, 6, 64), NB_K(4, 1, 0, 3, 64),
-    NB_K(4, 1, 0, 5, 64), NB_K(3, 1, 0, 5, 64), NB_K(3, 1, 0, 6, 64), NB_K(2, 1, 0, 8, 64), NB_K(3, 1, 0, 4, 64),
+    // tuning set (NB_FORCE_CHUNK)
+    NB_K(4, 1, 0, 4, 32), NB_K(4, 1, 0, 4, 128), NB_K(3, 1, 0, 4, 64),
+    NB_KS(4, 1, 0), NB_KS(3, 1, 0), NB_KS(2, 1, 0), NB_KS(1, 1, 0),
+    NB_KS(4, 0, 1), NB_KS(3, 0, 1), NB_KS(2, 0, 1), NB_KS(1, 0, 1),
+    NB_KS(4, 1, 1), NB_KS(3, 1, 1), NB_KS(2, 1, 1), NB_KS(1, 1, 1),
 };
 #undef NB_K
+#undef NB_KS
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
 
-const KernelEntry* find_kernel(int r, int packed, int pot, int chunk = kFlushChunk, int minb = 4) {
+const KernelEntry* find_kernel(int r, int packed, int pot, int chunk = kFlushChunk, int minb = 4, int eqm = 0,
+                               int d2 = 0) {
     for (int k = 0; k < kNumKernels; ++k)
         if (kKernels[k].r == r && kKernels[k].packed == packed && kKernels[k].pot == pot && kKernels[k].chunk == chunk &&
-            kKernels[k].minb == minb)
+            kKernels[k].minb == minb && kKernels[k].eqm == eqm && kKernels[k].d2 == d2)
             return &kKernels[k];
     return nullptr;
 }
@@ -155,7 +165,11 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
     for (int q = 0; q < n_opts; ++q) {
         const int r = r_opts[q];
         if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 2 && r == 2)) continue;
-        const KernelEntry* ke = pot ? find_kernel(r, packed, 1) : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb);
+        // the specialised variants exist for the production shape only (packed, chunk 64, 4 CTAs/SM)
+        const bool special = !pot && packed == 1 && c->forced_chunk == kFlushChunk && c->forced_minb == 4;
+        const KernelEntry* ke = pot ? find_kernel(r, packed, 1)
+                                    : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb,
+                                                  special && c->uniform_mass ? 1 : 0, special && c->planar ? 1 : 0);
         if (!ke) continue;
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
@@ -212,6 +226,15 @@ __global__ void __launch_bounds__(256) pack_aos_kernel(StateView s, int which, i
     for (int k = 0; k < dim; ++k) out[(i - s.lo) * dim + k] = src[k][i];
 }
 
+// pair records of non-attracting rows: {x0,x1,y0,y1,z0,z1,m0,m1} = {far, far, 0, 0, 0, 0, 0, 0}
+__global__ void __launch_bounds__(256) fill_far_kernel(float* pk, long long n_pairs) {
+    const long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (q >= n_pairs) return;
+    float4* rec = reinterpret_cast<float4*>(pk) + 2 * q;
+    rec[0] = make_float4(kFarPacked, kFarPacked, 0.f, 0.f);
+    rec[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
 inline unsigned int blocks_for(long long n, int threads) { return (unsigned int)std::max<long long>(1, (n + threads - 1) / threads); }
 
 void free_bodies(nb_ctx* c) {
@@ -259,8 +282,11 @@ int size_for(nb_ctx* c, long long n) {
     NB_CUDA(cudaMemsetAsync(c->mass, 0, sizeof(float) * c->cap, c->stream));
     NB_CUDA(cudaMemsetAsync(c->pinned, 0, c->cap, c->stream));
     NB_CUDA(cudaMemsetAsync(c->live, 0, c->cap, c->stream));
-    NB_CUDA(cudaMemsetAsync(c->pk[0], 0, sizeof(float) * 4 * c->cap, c->stream));  // padding rows stay m = 0
-    NB_CUDA(cudaMemsetAsync(c->pk[1], 0, sizeof(float) * 4 * c->cap, c->stream));
+    // every row starts as a non-attracting row (x = kFarPacked, m = 0); padding rows stay that way
+    for (int g = 0; g < 2; ++g)
+        fill_far_kernel<<<blocks_for(c->cap / 2, 256), 256, 0, c->stream>>>(c->pk[g], c->cap / 2);
+    NB_CUDA(cudaGetLastError());
+    c->kernel_launches += 2;
 
     // launch plans: all sources in one launch, or (sharded) own sources first, the rest after the exchange
     const long long n_local = c->hi - c->lo;
@@ -358,6 +384,7 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
     if (const char* v = getenv("NB_FORCE_CHUNK")) c->forced_chunk = atoi(v);
     if (const char* v = getenv("NB_FORCE_MINB")) c->forced_minb = atoi(v);
+    if (const char* v = getenv("NB_FORCE_GENERIC")) c->force_generic = atoi(v) != 0;
     *out = c;
     return NB_OK;
 }
@@ -562,6 +589,7 @@ int launch_force(nb_ctx* c, int which, int mode, bool pot, double dt) {
     p.g = c->cfg.g;
     p.dt = dt;
     p.half_dt2 = 0.5 * dt * dt;  // Physics.hpp:300
+    p.eqm_mass = ke.eqm ? c->uniform_packed_mass : 1.0;
     const long long n_it = (n_local + (long long)kNT * pl.r - 1) / ((long long)kNT * pl.r);
     NB_TRY(prof_begin(c));
     ke.fn<<<(unsigned int)(n_it * pl.nseg), kNT, 0, c->stream>>>(p);
@@ -609,9 +637,22 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
     if (n < 0 || (n > 0 && (!pos || !vel || !mass))) return fail(NB_ERR_INVALID, "nb_upload: null array");
     NB_CUDA(cudaSetDevice(c->device));
     NB_CUDA(cudaStreamSynchronize(c->stream));
-    NB_TRY(size_for(c, n));
     c->dim = dim;
     c->mass_exp = mass_exponent(mass, n);
+    // kernel specialisations (NB_FORCE_GENERIC=1 disables them): one common mass over every body that can
+    // ever pass the gather filter, and z == 0 for reference-layout (2-D) uploads
+    float m0 = 0.f;
+    bool uniform = n > 0;
+    for (int64_t i = 0; i < n && uniform; ++i) {
+        const float m = mass[i];
+        if (!(m > 0.f && m <= 3.4028234663852886e38f)) continue;  // never live, Physics.hpp:198-199
+        if (m0 == 0.f) m0 = m;
+        uniform = (m == m0);
+    }
+    c->uniform_mass = uniform && m0 > 0.f && !c->force_generic;
+    c->uniform_packed_mass = (double)m0 * pow2d(-c->mass_exp);
+    c->planar = dim == 2 && !c->force_generic;
+    NB_TRY(size_for(c, n));
     c->acc_valid = false;
     c->packed_valid = false;
     c->step_diag_valid = false;

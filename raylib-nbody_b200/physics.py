@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libnbody_b200.so")
+LIB_PATH = os.environ.get("NB_LIB_PATH") or os.path.join(_PKG, "libnbody_b200.so")  # NB_LIB_PATH: developer A/B builds
 
 _dp = C.POINTER(C.c_double)
 _fp = C.POINTER(C.c_float)
