@@ -128,6 +128,9 @@ int nb_upload_state(nb_ctx* ctx, int64_t n, int dim, const double* pos, const do
  * NULL. Arrays are sized for all n bodies; a sharded context fills rows [lo,hi) only. */
 int nb_download(nb_ctx* ctx, double* pos_xy, double* vel_xy, double* acc_xy);
 int nb_download3(nb_ctx* ctx, double* pos_xyz, double* vel_xyz, double* acc_xyz);
+/* Same with the PrevAcceleration component (Components.hpp:19-21; written by the Verlet drift,
+ * Physics.hpp:303) as a fourth array; dim is 2 or 3. */
+int nb_download_state(nb_ctx* ctx, int dim, double* pos, double* vel, double* acc, double* acc_prev);
 
 int64_t nb_num_bodies(nb_ctx* ctx);
 int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);

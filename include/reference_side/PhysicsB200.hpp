@@ -1,0 +1,249 @@
+// PhysicsB200.hpp — the reference-side binding: what a raylib-nbody maintainer drops next to
+// src/systems/Physics.hpp to run the physics step on a B200 through libnbody_b200.so.
+//
+// It is written against the reference's own types (Position/Velocity/Acceleration/
+// PrevAcceleration/Mass/Pinned of src/components/Components.hpp:10-38, Config of
+// src/core/Config.hpp:11-50, Physics::Diagnostics of src/systems/Physics.hpp:22-30) and replaces
+//   Physics::register_systems     src/systems/Physics.hpp:32-64
+//   Physics::compute_gravity      :183-261        Physics::integrate          :263-327
+//   Physics::compute_diagnostics  :117-177        Physics::zero_net_momentum  :66-85
+// by gather -> C-ABI call -> scatter. No reference code is copied: the reference keeps
+// Collision::resolve (out of scope), trails, UI and rendering.
+//
+// Device residency: the shim keeps a host mirror of what it last scattered.
+// When a frame's gather equals the mirror nothing was edited from outside (UI, drag, merge,
+// scenario load), the device state is still authoritative and no upload happens; any
+// difference re-uploads everything. Row order is flecs iteration order of one w.each.
+//
+// Build: add include/ of this repo to the include path, link libnbody_b200.so.
+#pragma once
+
+#include <flecs.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "components/Components.hpp"
+#include "core/Config.hpp"
+#include "systems/Collision.hpp"
+#include "systems/Physics.hpp"
+
+#include "nbody_b200.h"
+
+namespace nbody {
+
+class PhysicsB200 {
+public:
+    using Diagnostics = Physics::Diagnostics;
+
+    // Flat copy of the physics components of every body, in flecs iteration order.
+    struct Bodies {
+        std::vector<double> pos, vel, acc, acc_prev;  // 2 doubles per body (DVec2)
+        std::vector<float> mass;
+        std::vector<uint8_t> pinned;
+        size_t size() const { return mass.size(); }
+        bool same_inputs(const Bodies& o) const {
+            // bitwise: NaN payloads and -0.0 count as edits too
+            return mass.size() == o.mass.size() && bytes_equal(pos, o.pos) && bytes_equal(vel, o.vel) &&
+                   bytes_equal(mass, o.mass) && bytes_equal(pinned, o.pinned);
+        }
+        template <class T>
+        static bool bytes_equal(const std::vector<T>& a, const std::vector<T>& b) {
+            return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(T)) == 0);
+        }
+    };
+
+    // One per world; stored as a flecs singleton by register_systems.
+    struct Device {
+        nb_ctx* ctx = nullptr;
+        Bodies mirror;            // what the device holds, as last scattered / uploaded
+        bool resident = false;    // mirror matches device state
+        nb_config applied{};
+        bool config_applied = false;
+        long long uploads = 0, frames = 0;
+    };
+
+    static void check(int status, const char* what) {
+        if (status != NB_OK) throw std::runtime_error(std::string(what) + ": " + nb_last_error());
+    }
+
+    static Bodies gather(const flecs::world& w) {
+        Bodies b;
+        w.each([&](const Position& p, const Velocity& v, const Acceleration& a, const PrevAcceleration& a0,
+                   const Mass& m, const Pinned& pin) {
+            b.pos.push_back(p.value.x); b.pos.push_back(p.value.y);
+            b.vel.push_back(v.value.x); b.vel.push_back(v.value.y);
+            b.acc.push_back(a.value.x); b.acc.push_back(a.value.y);
+            b.acc_prev.push_back(a0.value.x); b.acc_prev.push_back(a0.value.y);
+            b.mass.push_back(m.value);
+            b.pinned.push_back(pin.value ? 1 : 0);
+        });
+        return b;
+    }
+
+    // Write the device state back into the components (Physics.hpp:260 and the in-place writes
+    // of :276-323). `what`: bit 0 pos+vel, bit 1 acc, bit 2 acc_prev.
+    static void scatter(const flecs::world& w, const Bodies& b, int what) {
+        size_t i = 0;
+        w.each([&](Position& p, Velocity& v, Acceleration& a, PrevAcceleration& a0, const Mass&, const Pinned&) {
+            if (what & 1) {
+                p.value = DVec2{b.pos[2 * i], b.pos[2 * i + 1]};
+                v.value = DVec2{b.vel[2 * i], b.vel[2 * i + 1]};
+            }
+            if (what & 2) a.value = DVec2{b.acc[2 * i], b.acc[2 * i + 1]};
+            if (what & 4) a0.value = DVec2{b.acc_prev[2 * i], b.acc_prev[2 * i + 1]};
+            ++i;
+        });
+    }
+
+    static void apply_config(Device& d, const Config& cfg) {
+        nb_config c;
+        c.g = cfg.g;
+        c.softening = cfg.softening;
+        c.max_speed = cfg.max_speed;
+        c.integrator = cfg.integrator == 0 ? NB_INTEGRATOR_EULER : NB_INTEGRATOR_VERLET;  // Physics.hpp:273,294
+        c.max_substep = cfg.max_substep;
+        c.max_substeps_per_frame = cfg.max_substeps_per_frame;
+        if (d.config_applied && std::memcmp(&c, &d.applied, sizeof(c)) == 0) return;
+        check(nb_set_config(d.ctx, &c), "nb_set_config");
+        d.applied = c;
+        d.config_applied = true;
+    }
+
+    // Make the device hold the world's current bodies; returns the gathered copy.
+    static Bodies sync(const flecs::world& w, Device& d) {
+        Bodies now = gather(w);
+        if (!(d.resident && now.same_inputs(d.mirror))) {
+            // external edit (or first frame): Acceleration is not trusted to equal a(x), exactly
+            // like the reference's gravity system recomputing it every frame (Physics.hpp:45-48)
+            check(nb_upload_state(d.ctx, (int64_t)now.size(), 2, now.pos.data(), now.vel.data(), nullptr,
+                                  now.mass.data(), now.pinned.data()),
+                  "nb_upload_state");
+            d.uploads++;
+            d.mirror = now;
+            d.resident = true;
+        }
+        return now;
+    }
+
+    static void pull(Device& d, Bodies& b, bool with_prev) {
+        check(nb_download_state(d.ctx, 2, b.pos.data(), b.vel.data(), b.acc.data(),
+                                with_prev ? b.acc_prev.data() : nullptr),
+              "nb_download_state");
+    }
+
+    // ---- the reference statics, one by one (same names, arguments and side effects) --------
+
+    // Physics::compute_diagnostics, Physics.hpp:117-177. G and eps2 come from Config on the
+    // device side (the reference's callers always pass cfg->g and cfg->softening^2, :38-40).
+    static bool compute_diagnostics(const flecs::world& w, Device& d, Diagnostics& out) {
+        out = Diagnostics{};
+        auto* cfg = w.get_mut<Config>();
+        apply_config(d, *cfg);
+        sync(w, d);
+        nb_diag r;
+        check(nb_compute_diagnostics(d.ctx, &r), "nb_compute_diagnostics");
+        if (!r.ok) {  // Physics.hpp:140-145,155-159,170-175: auto-pause, zeroed struct
+            cfg->paused = true;
+            out.ok = false;
+            return false;
+        }
+        out.kinetic = r.kinetic;
+        out.potential = r.potential;
+        out.energy = r.energy;
+        out.momentum = DVec2{r.momentum[0], r.momentum[1]};
+        out.com = DVec2{r.com[0], r.com[1]};
+        out.totalMass = r.total_mass;
+        out.ok = true;
+        return true;
+    }
+
+    // Physics::compute_gravity, Physics.hpp:183-261 (always the direct sum; bh_threshold is ignored).
+    static void compute_gravity(const flecs::world& w, Device& d) {
+        apply_config(d, *w.get<Config>());
+        Bodies b = sync(w, d);
+        if (b.size() == 0) return;
+        check(nb_compute_gravity(d.ctx), "nb_compute_gravity");
+        pull(d, b, false);
+        scatter(w, b, 2);
+        d.mirror.acc = b.acc;
+    }
+
+    // Physics::integrate, Physics.hpp:263-327: advances with whatever Acceleration holds.
+    static void integrate(const flecs::world& w, Device& d, float dt) {
+        const Config& cfg = *w.get<Config>();
+        apply_config(d, cfg);
+        Bodies b = gather(w);
+        if (b.size() == 0) return;
+        check(nb_upload_state(d.ctx, (int64_t)b.size(), 2, b.pos.data(), b.vel.data(), b.acc.data(), b.mass.data(),
+                              b.pinned.data()),
+              "nb_upload_state");
+        d.uploads++;
+        check(nb_integrate(d.ctx, dt), "nb_integrate");
+        const bool verlet = cfg.integrator != 0;
+        pull(d, b, verlet);
+        scatter(w, b, verlet ? 7 : 1);
+        d.mirror = b;
+        d.resident = true;
+    }
+
+    // Physics::zero_net_momentum, Physics.hpp:66-85.
+    static void zero_net_momentum(const flecs::world& w, Device& d) {
+        Bodies b = sync(w, d);
+        if (b.size() == 0) return;
+        check(nb_zero_net_momentum(d.ctx), "nb_zero_net_momentum");
+        pull(d, b, false);
+        scatter(w, b, 1);
+        d.mirror.vel = b.vel;
+    }
+
+    // ---- the frame, Physics.hpp:32-64 -------------------------------------------------------
+    // sysA = reference system 1 (collisions stay reference CPU code; diagnostics on the device),
+    // sysB = reference systems 2+3 fused: one nb_step evaluates gravity and integrates, which is
+    // what the gravity system followed by integrate() computes. Trails (system 4) stay with the
+    // reference's renderer.
+    static void register_systems(const flecs::world& w, int device = 0) {
+        Device d;
+        check(nb_create(device, &d.ctx), "nb_create");
+        w.set<Device>(d);
+
+        w.system<>().kind(flecs::OnUpdate).iter([&](flecs::iter&) {
+            auto* cfg = w.get<Config>();
+            if (!cfg || cfg->paused) return;
+            nbody::systems::Collision::resolve(w);
+            Diagnostics diag{};
+            diag.ok = compute_diagnostics(w, *w.get_mut<Device>(), diag);
+            w.set<Diagnostics>(diag);
+        });
+
+        w.system<>().kind(flecs::OnUpdate).iter([&](const flecs::iter& it) {
+            const Config& cfg = *w.get<Config>();
+            if (cfg.paused) return;
+            Device& dev = *w.get_mut<Device>();
+            apply_config(dev, cfg);
+            const float baseDt = cfg.use_fixed_dt ? cfg.fixed_dt : (float)it.delta_time();
+            const float dtEff = baseDt * std::max(0.0f, cfg.time_scale);  // Physics.hpp:54-55
+            Bodies b = sync(w, dev);  // merges flushed at the end of sysA show up here as an edit
+            if (b.size() == 0) return;
+            check(nb_step(dev.ctx, dtEff, 1), "nb_step");
+            const bool verlet = cfg.integrator != 0;
+            pull(dev, b, verlet);
+            scatter(w, b, verlet ? 7 : 3);
+            dev.mirror = b;
+            dev.frames++;
+        });
+    }
+
+    static void shutdown(const flecs::world& w) {
+        if (auto* d = w.get_mut<Device>(); d && d->ctx) {
+            nb_destroy(d->ctx);
+            d->ctx = nullptr;
+        }
+    }
+};
+
+}  // namespace nbody

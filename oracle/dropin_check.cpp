@@ -1,0 +1,200 @@
+// oracle/dropin_check.cpp — TEST INFRASTRUCTURE (run by tests/test_gpu_dropin.py on a B200).
+//
+// Proves the drop-in claim end to end: two flecs worlds with the reference's own components and
+// Config; world R runs the UNMODIFIED reference systems (Physics::register_systems,
+// src/systems/Physics.hpp:32-64, compiled from /root/reference where it lies), world B runs
+// include/reference_side/PhysicsB200.hpp (gather -> libnbody_b200.so -> scatter). Same inputs,
+// same world.progress() calls, same external edits; the components are compared afterwards.
+// Built by oracle/Makefile into oracle/_ref/dropin_check (needs the reference's headers).
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <numbers>
+#include <random>
+#include <tuple>
+#include <vector>
+
+#include <flecs.h>
+#include <raylib-cpp.hpp>
+#include <raymath.h>
+
+#include "reference_side/PhysicsB200.hpp"
+
+using nbody::Physics;
+using nbody::PhysicsB200;
+
+namespace {
+
+struct Snapshot {
+    std::vector<double> pos, vel, acc, acc_prev;
+};
+
+Snapshot snap(const flecs::world& w) {
+    Snapshot s;
+    w.each([&](const Position& p, const Velocity& v, const Acceleration& a, const PrevAcceleration& a0) {
+        s.pos.push_back(p.value.x); s.pos.push_back(p.value.y);
+        s.vel.push_back(v.value.x); s.vel.push_back(v.value.y);
+        s.acc.push_back(a.value.x); s.acc.push_back(a.value.y);
+        s.acc_prev.push_back(a0.value.x); s.acc_prev.push_back(a0.value.y);
+    });
+    return s;
+}
+
+bool bitwise(const std::vector<double>& a, const std::vector<double>& b) {
+    return a.size() == b.size() && std::memcmp(a.data(), b.data(), a.size() * sizeof(double)) == 0;
+}
+
+double max_rel(const std::vector<double>& a, const std::vector<double>& b) {
+    if (a.size() != b.size()) return INFINITY;
+    double scale = 0.0, diff = 0.0;
+    for (size_t i = 0; i < a.size(); ++i) {
+        scale = std::max(scale, std::fabs(b[i]));
+        diff = std::max(diff, std::fabs(a[i] - b[i]));
+    }
+    return scale > 0.0 ? diff / scale : diff;
+}
+
+void make_config(flecs::world& w, int integrator) {
+    // flecs' C++ layer caches component ids per type across worlds: register every component in the
+    // same order in both worlds so the twin worlds agree on them
+    w.component<Config>(); w.component<Position>(); w.component<Velocity>(); w.component<Acceleration>();
+    w.component<PrevAcceleration>(); w.component<Mass>(); w.component<Pinned>(); w.component<Radius>();
+    w.component<Density>(); w.component<Tint>(); w.component<Trail>(); w.component<Selectable>();
+    w.component<Selected>(); w.component<Draggable>(); w.component<Physics::Diagnostics>();
+    w.component<PhysicsB200::Device>();
+    Config cfg{};
+    cfg.bh_threshold = INT_MAX;  // reference world: force the direct-sum branch (Physics.hpp:212)
+    cfg.use_fixed_dt = true;
+    cfg.draw_trails = false;
+    cfg.integrator = integrator;
+    w.set<Config>(cfg);
+}
+
+void add_disk(flecs::world& w, int n, unsigned seed, float softening) {
+    std::mt19937_64 rng(seed);
+    std::uniform_real_distribution<double> u(0.0, 1.0);
+    const double R = 3.844e8;
+    for (int i = 0; i < n; ++i) {
+        const double r = R * std::sqrt(u(rng)), th = 2.0 * std::numbers::pi * u(rng);
+        const float x = (float)(r * std::cos(th)), y = (float)(r * std::sin(th));
+        const float vx = (float)(-300.0 * std::sin(th)), vy = (float)(300.0 * std::cos(th));
+        w.entity()
+            .set<Position>({DVec2{x, y}})
+            .set<Velocity>({DVec2{vx, vy}})
+            .set<Acceleration>({DVec2{0.0, 0.0}})
+            .set<PrevAcceleration>({DVec2{0.0, 0.0}})
+            .set<Mass>({7.342e22f})
+            .set<Pinned>({i % 97 == 0})
+            .set<Radius>({0.0});  // Collision::resolve never merges (Collision.hpp:29,83-85)
+    }
+    w.get_mut<Config>()->softening = softening;
+}
+
+void neutralise_collisions(flecs::world& w) {
+    std::vector<flecs::entity> es;
+    w.each([&](flecs::entity e, Position&) { es.push_back(e); });
+    for (auto& e : es) e.set<Radius>({0.0});
+}
+
+int failures = 0;
+void expect(bool ok, const char* what) {
+    std::printf("  [%s] %s\n", ok ? "ok" : "FAIL", what);
+    if (!ok) ++failures;
+}
+
+}  // namespace
+
+int main() {
+    // ---- A: config 1, the built-in three-body seed; n <= 512 runs the FP64 exact path ----------
+    for (int integrator : {1, 0}) {
+        flecs::world wr, wb;
+        make_config(wr, integrator);
+        make_config(wb, integrator);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0);
+        Physics::reset_scenario(wr);
+        Physics::reset_scenario(wb);  // the seed itself is host-side scenario code (same call on both)
+        neutralise_collisions(wr);
+        neutralise_collisions(wb);
+        const float dt = wr.get<Config>()->fixed_dt;
+        for (int f = 0; f < 2000; ++f) {
+            wr.progress(dt);
+            wb.progress(dt);
+        }
+        const Snapshot r = snap(wr), b = snap(wb);
+        std::printf("three-body seed, integrator %d, 2000 frames\n", integrator);
+        expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel), "positions and velocities bit-identical");
+        expect(bitwise(r.acc, b.acc), "accelerations bit-identical");
+        if (integrator == 1) expect(bitwise(r.acc_prev, b.acc_prev), "previous accelerations bit-identical");
+        const auto* dr = wr.get<Physics::Diagnostics>();
+        const auto* db = wb.get<Physics::Diagnostics>();
+        expect(dr && db && dr->ok && db->ok && std::fabs(dr->energy - db->energy) <= 1e-12 * std::fabs(dr->energy) &&
+                   dr->totalMass == db->totalMass,
+               "Diagnostics singleton matches (energy to 1e-12)");
+        const auto* dev = wb.get<PhysicsB200::Device>();
+        std::printf("  uploads %lld over %lld frames\n", dev->uploads, dev->frames);
+        expect(dev->uploads == 1, "state stayed device-resident (one upload)");
+        PhysicsB200::shutdown(wb);
+    }
+
+    // ---- B: 2048-body disk on the FP32 path, external edits, integrator switch ---------------------
+    {
+        flecs::world wr, wb;
+        make_config(wr, 1);
+        make_config(wb, 1);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0);
+        add_disk(wr, 2048, 99, 2.0e6f);
+        add_disk(wb, 2048, 99, 2.0e6f);
+        for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->time_scale = 3.0e4f;  // dtEff = 250 s
+        const float dt = wr.get<Config>()->fixed_dt;
+        auto run = [&](int frames) {
+            for (int f = 0; f < frames; ++f) {
+                wr.progress(dt);
+                wb.progress(dt);
+            }
+        };
+        run(5);
+        // external edit, as the UI does (UI.hpp:195-210): same edit on both worlds
+        for (flecs::world* w : {&wr, &wb}) {
+            int k = 0;
+            w->each([&](Velocity& v, const Mass&) {
+                if (k++ == 7) v.value = DVec2{1234.5, -321.0};
+            });
+        }
+        run(3);
+        for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->integrator = 0;
+        run(3);
+        const Snapshot r = snap(wr), b = snap(wb);
+        std::printf("2048-body disk, Verlet x5, edit, Verlet x3, Euler x3\n");
+        const double ep = max_rel(b.pos, r.pos), ev = max_rel(b.vel, r.vel), ea = max_rel(b.acc, r.acc);
+        std::printf("  max |dpos|/max|pos| %.3e  max |dvel|/max|vel| %.3e  max |dacc|/max|acc| %.3e\n", ep, ev, ea);
+        // once positions have moved off the float grid the FP32 j-stream carries them to 2^-24 of the
+        // extent (32 m here) against a softening of 2e6 m: pair forces agree to ~1.6e-5
+        expect(ep < 1e-6 && ev < 5e-5 && ea < 1e-4, "trajectories within the FP32-path bounds");
+        const auto* dr = wr.get<Physics::Diagnostics>();
+        const auto* db = wb.get<Physics::Diagnostics>();
+        expect(dr && db && dr->ok && db->ok && std::fabs(dr->energy - db->energy) <= 2e-6 * std::fabs(dr->energy),
+               "Diagnostics energy within 2e-6");
+        const auto* dev = wb.get<PhysicsB200::Device>();
+        std::printf("  uploads %lld over %lld frames\n", dev->uploads, dev->frames);
+        expect(dev->uploads == 2, "one upload at start, one after the external edit, none otherwise");
+
+        // non-finite body: the reference pauses itself (Physics.hpp:140-145); so must the binding
+        for (flecs::world* w : {&wr, &wb}) {
+            int k = 0;
+            w->each([&](Position& p, const Mass&) {
+                if (k++ == 3) p.value.x = NAN;
+            });
+        }
+        run(1);
+        expect(wr.get<Config>()->paused && wb.get<Config>()->paused, "non-finite state auto-pauses both worlds");
+        expect(!wb.get<Physics::Diagnostics>()->ok, "Diagnostics.ok is false");
+        PhysicsB200::shutdown(wb);
+    }
+    std::printf(failures ? "DROPIN CHECK FAILED (%d)\n" : "DROPIN CHECK PASSED\n", failures);
+    return failures ? 1 : 0;
+}

@@ -218,11 +218,11 @@ __global__ void __launch_bounds__(256) unpack_aos_kernel(const double* pos, cons
     }
 }
 
-// which: 0 x, 1 v, 2 a -> out[(i - lo) * dim + k] for rows [lo,hi)
+// which: 0 x, 1 v, 2 a, 3 a0 -> out[(i - lo) * dim + k] for rows [lo,hi)
 __global__ void __launch_bounds__(256) pack_aos_kernel(StateView s, int which, int dim, double* out) {
     const long long i = s.lo + blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= s.hi) return;
-    double* const* src = which == 0 ? s.x : (which == 1 ? s.v : s.a);
+    double* const* src = which == 0 ? s.x : (which == 1 ? s.v : (which == 2 ? s.a : s.a0));
     for (int k = 0; k < dim; ++k) out[(i - s.lo) * dim + k] = src[k][i];
 }
 
@@ -691,16 +691,16 @@ extern "C" int nb_upload_state(nb_ctx* c, int64_t n, int dim, const double* pos,
     return upload_dim(c, n, pos, vel, mass, pinned, dim, acc);
 }
 
-static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int dim) {
+static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int dim, double* acc_prev = nullptr) {
     if (!c) return fail(NB_ERR_INVALID, "nb_download: null context");
     NB_CUDA(cudaSetDevice(c->device));
     const long long n_local = c->hi - c->lo;
     if (n_local <= 0) return NB_OK;
     const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n_local;
-    NB_TRY(ensure_staging(c, 3 * vec_bytes));
-    double* out[3] = {pos, vel, acc};
+    NB_TRY(ensure_staging(c, 4 * vec_bytes));
+    double* out[4] = {pos, vel, acc, acc_prev};
     const StateView s = c->view();
-    for (int w = 0; w < 3; ++w) {
+    for (int w = 0; w < 4; ++w) {
         if (!out[w]) continue;
         double* d = static_cast<double*>(c->staging) + (size_t)w * dim * n_local;
         pack_aos_kernel<<<blocks_for(n_local, 256), 256, 0, c->stream>>>(s, w, dim, d);
@@ -716,6 +716,10 @@ extern "C" int nb_download(nb_ctx* c, double* pos_xy, double* vel_xy, double* ac
 }
 extern "C" int nb_download3(nb_ctx* c, double* pos_xyz, double* vel_xyz, double* acc_xyz) {
     return download_dim(c, pos_xyz, vel_xyz, acc_xyz, 3);
+}
+extern "C" int nb_download_state(nb_ctx* c, int dim, double* pos, double* vel, double* acc, double* acc_prev) {
+    if (dim != 2 && dim != 3) return fail(NB_ERR_INVALID, "nb_download_state: dim must be 2 or 3");
+    return download_dim(c, pos, vel, acc, dim, acc_prev);
 }
 
 // ---------------------------------------------------------------------------------------

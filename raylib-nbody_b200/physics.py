@@ -56,7 +56,7 @@ class Diagnostics:
 
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
-           "nb_download3", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
+           "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
@@ -257,6 +257,13 @@ class Physics:
         out = [np.zeros((n, self.dim)) if want else None for want in (pos, vel, acc)]
         fn = self._L.nb_download if self.dim == 2 else self._L.nb_download3
         _check(fn(self._h, *[None if a is None else a.ctypes.data_as(_dp) for a in out]))
+        return tuple(out)
+
+    def download_state(self):
+        """(pos, vel, acc, acc_prev): the four DVec2 components of Components.hpp:10-21."""
+        n = self.num_bodies()
+        out = [np.zeros((n, self.dim)) for _ in range(4)]
+        _check(self._L.nb_download_state(self._h, self.dim, *[a.ctypes.data_as(_dp) for a in out]))
         return tuple(out)
 
     def num_bodies(self):
