@@ -17,7 +17,10 @@
 
 namespace nb {
 
-constexpr int kTileBodies = 512;          // j-bodies per shared-memory stage (8 KB)
+#ifndef NB_TILE
+#define NB_TILE 512
+#endif
+constexpr int kTileBodies = NB_TILE;      // j-bodies per shared-memory stage (16 B each: 8 KB)
 #ifndef NB_STAGES
 #define NB_STAGES 2
 #endif

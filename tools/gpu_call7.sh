@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out; : > gpurun_out/ring_ab.txt
-for v in nt256 nt512 main; do
+for v in t128 t256 t1024 t1024s3 main; do
   for g in 0 1; do
     if [ $v = main ]; then unset NB_LIB_PATH; else export NB_LIB_PATH=$PWD/tools/ubench/variants/$v.so; fi
     echo "== $v generic=$g" >> gpurun_out/ring_ab.txt
