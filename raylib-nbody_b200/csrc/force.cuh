@@ -73,6 +73,8 @@ struct Target<true, POT, EQM, D2> {
         nxi = f2_make(-x, -x); nyi = f2_make(-y, -y); nzi = f2_make(-z, -z);
         ax = ay = az = ph = f2_make(0.f, 0.f);
     }
+    // mj: the sources' masses; for EQM kernels only read when MASKED, as a {0|1, 0|1} self-term mask
+    template <bool MASKED = false>
     __device__ __forceinline__ void interact(f2 xj, f2 yj, f2 zj, f2 mj, f2 eps2) {
         const f2 dx = f2_add(xj, nxi), dy = f2_add(yj, nyi);
         f2 r2 = f2_fma(dx, dx, eps2);
@@ -90,7 +92,10 @@ struct Target<true, POT, EQM, D2> {
         ax = f2_fma(s, dx, ax);
         ay = f2_fma(s, dy, ay);
         if (!D2) az = f2_fma(s, dz, az);
-        if (POT) ph = f2_fma(mj, f2_mul(w, r2), ph);
+        if (POT) {
+            if (EQM && !MASKED) ph = f2_fma(w, r2, ph);  // 1 / r (non-attracting rows: w = 0)
+            else ph = f2_fma(mj, f2_mul(w, r2), ph);    // m / r
+        }
     }
     // The even/odd-source halves are added in FP32 first: one commutative, sign-symmetric
     // rounding, so mirror-symmetric configurations (the reference's three-body seed,
@@ -117,7 +122,7 @@ __device__ __forceinline__ void chunk_interact(Target<PACKED, POT, EQM, D2> (&t)
         for (int u = 0; u < CH / 2; ++u) {
             const ulonglong2 A = *reinterpret_cast<const ulonglong2*>(rec + 2 * u);
             f2 xj{A.x}, yj{A.y}, zj{0ull}, mj{0ull};
-            constexpr bool kNeedM = !EQM || POT;
+            constexpr bool kNeedM = !EQM;
             const unsigned long long* B64 = reinterpret_cast<const unsigned long long*>(rec + 2 * u + 1);
             if (!D2 && kNeedM) {
                 const ulonglong2 B = *reinterpret_cast<const ulonglong2*>(rec + 2 * u + 1);
@@ -132,12 +137,12 @@ __device__ __forceinline__ void chunk_interact(Target<PACKED, POT, EQM, D2> (&t)
             for (int r = 0; r < R; ++r) {
                 f2 m = mj;
                 if (MASK) {
-                    float m0, m1;
-                    f2_split(mj, m0, m1);
+                    float m0 = 1.f, m1 = 1.f;
+                    if (!EQM) f2_split(mj, m0, m1);
                     const long long j0 = j_first + 2 * u;
                     m = f2_make(j0 == ti[r] ? 0.f : m0, j0 + 1 == ti[r] ? 0.f : m1);
                 }
-                t[r].interact(xj, yj, zj, m, e2);
+                t[r].template interact<MASK>(xj, yj, zj, m, e2);
             }
         }
     } else {

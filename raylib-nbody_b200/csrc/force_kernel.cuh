@@ -47,6 +47,7 @@ force_kernel(const __grid_constant__ StepParams p) {
     // scales of the generation being read and of the one the epilogue packs (common.cuh)
     Scale cur = scale_for(p.extent[(p.gen + kExtentSlots - 1) % kExtentSlots], p.mass_exp, p.g, p.softening);
     cur.acc_unit *= p.eqm_mass;
+    cur.pot_unit *= p.eqm_mass;
 
     // ---- targets ---------------------------------------------------------------------
     Target<PACKED, POT, EQM, D2> tg[R];

@@ -129,6 +129,7 @@ struct KernelEntry {
 #define NB_K(R, P, POT, MINB, CH) {R, P, POT, CH, MINB, 0, 0, force_kernel<kNT, R, (P) != 0, (POT) != 0, (MINB) / kCtaScale, CH>}
 // specialised packed force-only kernels: E uniform mass (no m*w multiply), D z == 0 (reference 2-D uploads)
 #define NB_KS(R, E, D) {R, 1, 0, 64, 4, E, D, force_kernel<kNT, R, true, false, 4 / kCtaScale, 64, (E) != 0, (D) != 0>}
+#define NB_KSP(R, E, D) {R, 1, 1, 64, 4, E, D, force_kernel<kNT, R, true, true, 4 / kCtaScale, 64, (E) != 0, (D) != 0>}
 const KernelEntry kKernels[] = {
     // production set: flush chunk kFlushChunk (64), 4 CTAs/SM
     NB_K(4, 1, 0, 4, 64), NB_K(2, 1, 0, 4, 64), NB_K(1, 1, 0, 4, 64),
@@ -139,9 +140,13 @@ const KernelEntry kKernels[] = {
     NB_KS(4, 1, 0), NB_KS(3, 1, 0), NB_KS(2, 1, 0), NB_KS(1, 1, 0),
     NB_KS(4, 0, 1), NB_KS(3, 0, 1), NB_KS(2, 0, 1), NB_KS(1, 0, 1),
     NB_KS(4, 1, 1), NB_KS(3, 1, 1), NB_KS(2, 1, 1), NB_KS(1, 1, 1),
+    // with the fused potential (nb_step_with_diagnostics)
+    NB_KSP(3, 0, 0), NB_KSP(3, 1, 0), NB_KSP(2, 1, 0), NB_KSP(1, 1, 0), NB_KSP(3, 0, 1), NB_KSP(2, 0, 1), NB_KSP(1, 0, 1),
+    NB_KSP(3, 1, 1), NB_KSP(2, 1, 1), NB_KSP(1, 1, 1),
 };
 #undef NB_K
 #undef NB_KS
+#undef NB_KSP
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
 
 const KernelEntry* find_kernel(int r, int packed, int pot, int chunk = kFlushChunk, int minb = 4, int eqm = 0,
@@ -159,17 +164,17 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
     double best_score = -1.0;
     const int packed = c->forced_packed >= 0 ? c->forced_packed : 1;
     const int r_opts_force[] = {4, 3, 2, 1};
-    const int r_opts_pot[] = {2, 1};
+    const int r_opts_pot[] = {3, 2, 1};
     const int* r_opts = pot ? r_opts_pot : r_opts_force;
-    const int n_opts = pot ? 2 : 4;
+    const int n_opts = pot ? 3 : 4;
     for (int q = 0; q < n_opts; ++q) {
         const int r = r_opts[q];
-        if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 2 && r == 2)) continue;
+        if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 3 && r == 3)) continue;
         // the specialised variants exist for the production shape only (packed, chunk 64, 4 CTAs/SM)
-        const bool special = !pot && packed == 1 && c->forced_chunk == kFlushChunk && c->forced_minb == 4;
-        const KernelEntry* ke = pot ? find_kernel(r, packed, 1)
-                                    : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb,
-                                                  special && c->uniform_mass ? 1 : 0, special && c->planar ? 1 : 0);
+        const bool special = packed == 1 && (pot || (c->forced_chunk == kFlushChunk && c->forced_minb == 4));
+        const int eqm = special && c->uniform_mass ? 1 : 0, d2 = special && c->planar ? 1 : 0;
+        const KernelEntry* ke = pot ? find_kernel(r, packed, 1, kFlushChunk, 4, eqm, d2)
+                                    : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb, eqm, d2);
         if (!ke) continue;
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
