@@ -382,8 +382,10 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     NB_CUDA(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
     NB_CUDA(cudaMalloc(&c->extent, sizeof(unsigned int) * (kExtentSlots + 4)));
     NB_CUDA(cudaMemset(c->extent, 0, sizeof(unsigned int) * (kExtentSlots + 4)));
-    NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * 64));
-    NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * 64 * 16));
+    // [0,16): this rank's fixed-order sums; [16, 16 + kDiagValues * world): every rank's, all-gathered
+    const size_t totals_len = 16 + (size_t)kDiagValues * world + 16;
+    NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * totals_len));
+    NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * totals_len));
     if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
     if (const char* v = getenv("NB_FORCE_PACKED")) c->forced_packed = atoi(v);
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);

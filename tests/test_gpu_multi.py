@@ -30,14 +30,15 @@ def _free_port():
 
 
 def _worker(rank, world, port, n, integ, out_dir):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))  # NCCL/gloo bootstrap address only
     sys.path.insert(0, ROOT)
     import torch
     import torch.distributed as dist
     import __graft_entry__ as ge
     pkg = ge.load_package()
     torch.cuda.set_device(rank)
-    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank),
+                            init_method="file://" + os.path.join(out_dir, "rendezvous"))  # no TCP store port to collide on
     try:
         pos, vel, mass = pkg.scenarios.plummer(n, seed=17, dim=3)
         eps = 3.844e8 / np.sqrt(n)
@@ -64,7 +65,7 @@ def _worker(rank, world, port, n, integ, out_dir):
 
 
 @pytest.mark.parametrize("integ", [1, 0])
-@pytest.mark.parametrize("world,n", [(2, 20000), (2, 700)])
+@pytest.mark.parametrize("world,n", [(2, 20000), (2, 700), (8, 9000), (3, 5000)])
 def test_sharded_matches_single_gpu(pkg, tmp_path, world, n, integ):
     if _n_gpus() < world:
         pytest.skip(f"needs {world} GPUs")

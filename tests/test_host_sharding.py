@@ -27,7 +27,8 @@ def _worker(rank, world, port, n, out_dir):
     import torch.distributed as dist
     import __graft_entry__ as ge
     pkg = ge.load_package()
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    dist.init_process_group("gloo", rank=rank, world_size=world,
+                            init_method="file://" + os.path.join(out_dir, "rendezvous"))  # no TCP store port to collide on
     try:
         # rank 0 draws the id; everyone must end up with the same 128 bytes
         uid = pkg.sharded.broadcast_unique_id(dist, make_id=lambda: bytes(range(128)))
