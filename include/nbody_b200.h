@@ -170,6 +170,16 @@ int nb_compute_diagnostics(nb_ctx* ctx, nb_diag* out);
 /* Physics::zero_net_momentum (Physics.hpp:66-85). */
 int nb_zero_net_momentum(nb_ctx* ctx);
 
+/* Detection phase of Collision::resolve (src/systems/Collision.hpp:63-84) on the bodies the
+ * context holds: the number of pairs i < j, both passing its input filter (finite position, finite
+ * mass > 0), with dist2 <= (r_i + r_j)^2 evaluated in the reference's FP64 operation order, and
+ * (first_pair, may be NULL) the first such pair in the reference's visiting order, (-1,-1) if none.
+ * `radius` is the caller's Collision::radius_of per body (Radius component, or mass + density,
+ * Collision.hpp:28-35). Zero overlaps means resolve() would change nothing this frame, so the
+ * binding only runs the reference's merge code on frames where the count is non-zero.
+ * Single-GPU contexts. Synchronises. */
+int nb_count_overlaps(nb_ctx* ctx, const double* radius, int64_t* n_overlaps, int64_t* first_pair);
+
 /* Substep plan of Physics.hpp:268-271 (float arithmetic). Host-only helper. */
 int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub);
 

@@ -65,6 +65,7 @@ public:
         nb_config applied{};
         bool config_applied = false;
         long long uploads = 0, frames = 0;
+        long long collision_checks = 0, collision_frames = 0;  // device detections / frames that ran the CPU merge
     };
 
     static void check(int status, const char* what) {
@@ -201,8 +202,30 @@ public:
         d.mirror.vel = b.vel;
     }
 
+    // Collision::resolve (Collision.hpp:49-203) with its O(N^2) detection phase on the device: the
+    // reference's own merge code runs only on frames where some pair overlaps (nb_count_overlaps
+    // evaluates Collision.hpp:76-84 exactly), so merge semantics are the reference's, bit for bit.
+    static void resolve_collisions(const flecs::world& w, Device& d) {
+        apply_config(d, *w.get<Config>());
+        Bodies b = sync(w, d);
+        if (b.size() < 2) return;  // Collision.hpp:70
+        std::vector<double> radius;
+        radius.reserve(b.size());
+        w.each([&](const flecs::entity e, const Position&, const Velocity&, const Acceleration&,
+                   const PrevAcceleration&, const Mass& m, const Pinned&) {
+            radius.push_back(nbody::systems::Collision::radius_of(e, m));  // Collision.hpp:28-35
+        });
+        int64_t overlaps = 0;
+        check(nb_count_overlaps(d.ctx, radius.data(), &overlaps, nullptr), "nb_count_overlaps");
+        d.collision_checks++;
+        if (overlaps == 0) return;
+        d.collision_frames++;
+        nbody::systems::Collision::resolve(w);  // edits components; the next sync() sees them and re-uploads
+    }
+
     // ---- the frame, Physics.hpp:32-64 -------------------------------------------------------
-    // sysA = reference system 1 (collisions stay reference CPU code; diagnostics on the device),
+    // sysA = reference system 1 (collision detection and diagnostics on the device; the merge itself
+    // stays reference CPU code and only runs when a pair overlaps),
     // sysB = reference systems 2+3 fused: one nb_step evaluates gravity and integrates, which is
     // what the gravity system followed by integrate() computes. Trails (system 4) stay with the
     // reference's renderer.
@@ -214,7 +237,7 @@ public:
         w.system<>().kind(flecs::OnUpdate).iter([&](flecs::iter&) {
             auto* cfg = w.get<Config>();
             if (!cfg || cfg->paused) return;
-            nbody::systems::Collision::resolve(w);
+            resolve_collisions(w, *w.get_mut<Device>());
             Diagnostics diag{};
             diag.ok = compute_diagnostics(w, *w.get_mut<Device>(), diag);
             w.set<Diagnostics>(diag);

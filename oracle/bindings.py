@@ -109,6 +109,15 @@ class Oracle:
         ok = fn(C.c_int64(n), _d(pos), _d(vel), _f(mass), C.c_double(g), C.c_double(eps2), _d(out))
         return out, bool(ok)
 
+    def count_overlaps(self, pos, mass, radius):
+        """Detection phase of Collision::resolve (Collision.hpp:63-84): (n_pairs, first_pair or None)."""
+        first = (C.c_int64 * 2)()
+        self.lib.orc_count_overlaps.restype = C.c_int64
+        n = self.lib.orc_count_overlaps(C.c_int64(pos.shape[0]), _d(np.ascontiguousarray(pos, np.float64)),
+                                        _f(np.ascontiguousarray(mass, np.float32)),
+                                        _d(np.ascontiguousarray(radius, np.float64)), first)
+        return int(n), ((first[0], first[1]) if n else None)
+
     def zero_net_momentum(self, vel, mass, pinned=None):
         n = vel.shape[0]
         self.lib.orc_zero_net_momentum(C.c_int64(n), _d(vel), _f(mass), _b(pinned))
@@ -168,6 +177,11 @@ class Reference:
 
     def reset_scenario(self):
         return self.lib.ref_reset_scenario(self.h)
+
+    def collision_resolve(self, radius):
+        """Collision::resolve with explicit Radius components; returns the number of bodies left."""
+        self.lib.ref_collision_resolve.restype = C.c_int64
+        return int(self.lib.ref_collision_resolve(self.h, _d(np.ascontiguousarray(radius, np.float64))))
 
     def num_bodies(self):
         return self.lib.ref_num_bodies(self.h)

@@ -73,7 +73,7 @@ void make_config(flecs::world& w, int integrator) {
     w.set<Config>(cfg);
 }
 
-void add_disk(flecs::world& w, int n, unsigned seed, float softening) {
+void add_disk(flecs::world& w, int n, unsigned seed, float softening, bool physical_radius = false) {
     std::mt19937_64 rng(seed);
     std::uniform_real_distribution<double> u(0.0, 1.0);
     const double R = 3.844e8;
@@ -81,14 +81,16 @@ void add_disk(flecs::world& w, int n, unsigned seed, float softening) {
         const double r = R * std::sqrt(u(rng)), th = 2.0 * std::numbers::pi * u(rng);
         const float x = (float)(r * std::cos(th)), y = (float)(r * std::sin(th));
         const float vx = (float)(-300.0 * std::sin(th)), vy = (float)(300.0 * std::cos(th));
-        w.entity()
-            .set<Position>({DVec2{x, y}})
-            .set<Velocity>({DVec2{vx, vy}})
-            .set<Acceleration>({DVec2{0.0, 0.0}})
-            .set<PrevAcceleration>({DVec2{0.0, 0.0}})
-            .set<Mass>({7.342e22f})
-            .set<Pinned>({i % 97 == 0})
-            .set<Radius>({0.0});  // Collision::resolve never merges (Collision.hpp:29,83-85)
+        auto e = w.entity()
+                     .set<Position>({DVec2{x, y}})
+                     .set<Velocity>({DVec2{vx, vy}})
+                     .set<Acceleration>({DVec2{0.0, 0.0}})
+                     .set<PrevAcceleration>({DVec2{0.0, 0.0}})
+                     .set<Mass>({7.342e22f})
+                     .set<Pinned>({i % 97 == 0});
+        // Radius{0}: Collision::resolve never merges (Collision.hpp:29,83-85); without the component
+        // the radius is derived from mass and density (1.47e6 m here, Collision.hpp:30-34)
+        if (!physical_radius) e.set<Radius>({0.0});
     }
     w.get_mut<Config>()->softening = softening;
 }
@@ -193,6 +195,32 @@ int main() {
         run(1);
         expect(wr.get<Config>()->paused && wb.get<Config>()->paused, "non-finite state auto-pauses both worlds");
         expect(!wb.get<Physics::Diagnostics>()->ok, "Diagnostics.ok is false");
+        PhysicsB200::shutdown(wb);
+    }
+    // ---- C: real radii: collision detection on the device, merges by the reference's own code ---------
+    {
+        flecs::world wr, wb;
+        make_config(wr, 1);
+        make_config(wb, 1);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0);
+        add_disk(wr, 400, 7, 2.0e6f, true);
+        add_disk(wb, 400, 7, 2.0e6f, true);
+        for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->time_scale = 3.0e4f;
+        const float dt = wr.get<Config>()->fixed_dt;
+        for (int f = 0; f < 40; ++f) {
+            wr.progress(dt);
+            wb.progress(dt);
+        }
+        const Snapshot r = snap(wr), b = snap(wb);
+        const auto* dev = wb.get<PhysicsB200::Device>();
+        std::printf("400-body disk with physical radii, 40 frames: %zu bodies left (reference %zu); device detections %lld, "
+                    "frames that ran the CPU merge %lld\n",
+                    b.pos.size() / 2, r.pos.size() / 2, dev->collision_checks, dev->collision_frames);
+        expect(r.pos.size() == b.pos.size() && r.pos.size() < 800, "same number of merges in both worlds");
+        expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel) && bitwise(r.acc, b.acc), "state bit-identical after merges");
+        expect(dev->collision_checks == 40 && dev->collision_frames >= 1 && dev->collision_frames < 40,
+               "the reference's O(N^2) collision pass ran only on the frames with an overlap");
         PhysicsB200::shutdown(wb);
     }
     std::printf(failures ? "DROPIN CHECK FAILED (%d)\n" : "DROPIN CHECK PASSED\n", failures);

@@ -304,3 +304,28 @@ void orc_seed_three_body(double g, double* pos, double* vel, float* mass, uint8_
     }
     orc_zero_net_momentum(3, vel, mass, pinned); /* :114 */
 }
+
+/* Detection phase of Collision::resolve, src/systems/Collision.hpp:63-84: bodies with finite
+ * position and finite mass > 0 (:63-65); for i < j: dx = xj - xi, dy = yj - yi, rsum = ri + rj,
+ * dist2 = dx*dx + dy*dy, overlap unless dist2 > rsum*rsum (:76-84). Returns the number of
+ * overlapping pairs and the first one in visiting order ((-1,-1) if none). No merge is applied:
+ * zero overlaps is exactly the case in which resolve() leaves the world untouched. */
+int64_t orc_count_overlaps(int64_t n, const double* pos, const float* mass, const double* radius,
+                           int64_t* first_pair) {
+    int64_t count = 0;
+    first_pair[0] = first_pair[1] = -1;
+    for (int64_t i = 0; i < n; ++i) {
+        if (!(isfinite(pos[2 * i]) && isfinite(pos[2 * i + 1]) && isfinite((double)mass[i])) || mass[i] <= 0.0f) continue;
+        for (int64_t j = i + 1; j < n; ++j) {
+            if (!(isfinite(pos[2 * j]) && isfinite(pos[2 * j + 1]) && isfinite((double)mass[j])) || mass[j] <= 0.0f) continue;
+            const double dx = pos[2 * j] - pos[2 * i];
+            const double dy = pos[2 * j + 1] - pos[2 * i + 1];
+            const double rsum = radius[i] + radius[j];
+            const double dist2 = dx * dx + dy * dy;
+            if (dist2 > rsum * rsum) continue;
+            if (count == 0) { first_pair[0] = i; first_pair[1] = j; }
+            ++count;
+        }
+    }
+    return count;
+}

@@ -117,6 +117,19 @@ void ref_load_bodies(void* h, int64_t n, const double* pos, const double* vel, c
     }
 }
 
+// Explicit per-body Radius components (Components.hpp:33-35), then the reference's collision pass
+// (Collision.hpp:49-203, merge mode). Returns the number of bodies left; used to pin the
+// oracle's detection: resolve() changes nothing exactly when no pair overlaps.
+int64_t ref_collision_resolve(void* h, const double* radius) {
+    auto* rw = static_cast<RefWorld*>(h);
+    for (size_t i = 0; i < rw->bodies.size(); ++i) rw->bodies[i].set<Radius>({radius[i]});
+    rw->w.defer_begin();  // as inside a flecs system: destruct() takes effect at defer_end (flecs.c:64517,64556)
+    nbody::systems::Collision::resolve(rw->w);
+    rw->w.defer_end();
+    collect_bodies(rw);
+    return static_cast<int64_t>(rw->bodies.size());
+}
+
 // Built-in three-body seed with momentum zeroing (Physics.hpp:87-115). Radius{0} is
 // added afterwards so a later ref_progress() cannot merge bodies.
 int64_t ref_reset_scenario(void* h) {

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <string>
 
+#include "collide.cuh"
 #include "ctx.cuh"
 #include "diag.cuh"
 #include "exact.cuh"
@@ -1050,6 +1051,41 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
     NB_CUDA(cudaGetLastError());
     c->step_diag_valid = false;
     // velocities changed: the gather filter may change, positions did not -> the j-stream stays valid
+    return NB_OK;
+}
+
+extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair) {
+    if (!c || !n_overlaps) return fail(NB_ERR_INVALID, "nb_count_overlaps: null");
+    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_count_overlaps: single-GPU contexts only (FP64 positions are not replicated)");
+    *n_overlaps = 0;
+    if (first_pair) first_pair[0] = first_pair[1] = -1;
+    if (c->n < 2) return NB_OK;  // Collision.hpp:70
+    if (!radius) return fail(NB_ERR_INVALID, "nb_count_overlaps: null radius array");
+    NB_CUDA(cudaSetDevice(c->device));
+    const size_t r_bytes = sizeof(double) * (size_t)c->n;
+    NB_TRY(ensure_staging(c, r_bytes + 16));
+    double* d_radius = static_cast<double*>(c->staging);
+    unsigned long long* d_res = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->staging) + r_bytes);
+    const unsigned long long init[2] = {0ull, ~0ull};
+    NB_CUDA(cudaMemcpyAsync(d_radius, radius, r_bytes, cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(d_res, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
+    const StateView s = c->view();
+    if (c->dim == 2)
+        overlap_kernel<true><<<blocks_for(c->n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
+            s.x[0], s.x[1], s.x[2], c->mass, d_radius, c->n, d_res);
+    else
+        overlap_kernel<false><<<blocks_for(c->n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
+            s.x[0], s.x[1], s.x[2], c->mass, d_radius, c->n, d_res);
+    NB_CUDA(cudaGetLastError());
+    c->kernel_launches++;
+    unsigned long long res[2];
+    NB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    *n_overlaps = (int64_t)res[0];
+    if (first_pair && res[0]) {
+        first_pair[0] = (int64_t)(res[1] / (unsigned long long)c->n);
+        first_pair[1] = (int64_t)(res[1] % (unsigned long long)c->n);
+    }
     return NB_OK;
 }
 

@@ -57,7 +57,7 @@ class Diagnostics:
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
-           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum",
+           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
@@ -91,6 +91,8 @@ def load_library(path=LIB_PATH):
     L.nb_free_pinned.argtypes = [C.c_void_p]
     L.nb_download.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_download3.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    L.nb_download_state.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
+    L.nb_count_overlaps.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_default_config.argtypes = [C.POINTER(Config)]
@@ -258,6 +260,15 @@ class Physics:
         fn = self._L.nb_download if self.dim == 2 else self._L.nb_download3
         _check(fn(self._h, *[None if a is None else a.ctypes.data_as(_dp) for a in out]))
         return tuple(out)
+
+    def count_overlaps(self, radius):
+        """Detection phase of Collision::resolve, Collision.hpp:63-84: (n_pairs, first_pair or None)."""
+        r = np.ascontiguousarray(radius, dtype=np.float64)
+        if r.shape != (self.num_bodies(),):
+            raise ValueError("radius must have one entry per body")
+        cnt, first = C.c_int64(), (C.c_int64 * 2)()
+        _check(self._L.nb_count_overlaps(self._h, r.ctypes.data_as(_dp), C.byref(cnt), first))
+        return cnt.value, ((first[0], first[1]) if cnt.value else None)
 
     def download_state(self):
         """(pos, vel, acc, acc_prev): the four DVec2 components of Components.hpp:10-21."""

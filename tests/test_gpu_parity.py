@@ -402,6 +402,42 @@ def test_specialised_kernels_match_oracle_and_generic(pkg, oracle_lib, ob, dim, 
     assert np.abs(accs[0][1][fin] - accs[1][1][fin]).max() / np.abs(pos).max() < 1e-7
 
 
+# ---- collision detection (detection phase) --------------------------------
+@pytest.mark.parametrize("n", [2, 257, 1000, 5000])
+def test_overlap_detection_matches_oracle(pkg, ph, oracle_lib, n):
+    """nb_count_overlaps == the oracle's restatement of Collision.hpp:63-84, bit-exact decisions:
+    same count and same first pair, with filtered bodies, huge and zero radii, and pairs placed
+    exactly on the dist2 == rsum^2 boundary (which the reference counts as overlapping)."""
+    rng = np.random.default_rng(n)
+    pos = (rng.standard_normal((n, 2)) * 1e8).astype(np.float32).astype(np.float64)
+    vel = np.zeros((n, 2))
+    mass = rng.uniform(1e22, 1e24, n).astype(np.float32)
+    if n > 10:
+        mass[3] = 0.0
+        mass[4] = -1.0
+        mass[6] = np.float32(np.inf)
+        pos[5, 1] = np.nan
+        pos[7, 0] = np.inf
+        pos[9] = pos[8] + np.array([3.0e6, 4.0e6])   # distance exactly 5e6
+    for scale in (0.0, 2.0e5, 2.5e6, 1.0e7):
+        rad = np.full(n, scale)
+        if n > 10 and scale == 2.5e6:
+            rad[8] = rad[9] = 2.5e6                      # rsum^2 == dist2: overlap (not dist2 > rsum^2)
+            rad[20] = 0.0
+        ph.upload(pos, vel, mass)
+        got = ph.count_overlaps(rad)
+        ref = oracle_lib.count_overlaps(pos, mass, rad)
+        assert got == ref, (n, scale, got, ref)
+    if n > 10:
+        rad = np.zeros(n)
+        rad[8] = rad[9] = 2.5e6
+        got = ph.count_overlaps(rad)
+        assert got == oracle_lib.count_overlaps(pos, mass, rad) and got[1] == (8, 9)   # boundary pair counts
+        rad[9] = 2.4999e6                                                              # just inside: no longer
+        got = ph.count_overlaps(rad)
+        assert got == oracle_lib.count_overlaps(pos, mass, rad) and got[1] != (8, 9)
+
+
 # ---- edge cases -------------------------------------------------------------------------------
 def test_empty_single_and_ragged_worlds(pkg, ph, oracle_lib):
     e2, e1 = np.zeros((0, 2)), np.zeros(0, np.float32)

@@ -163,3 +163,34 @@ def test_against_live_reference(oracle_lib, ob):
         do, oko = oracle_lib.compute_diagnostics(p, v, mass, softening=1.0e5)
         assert okr == oko and np.array_equal(dr, do)
     r.close()
+
+
+def test_overlap_detection_pins_to_reference_resolve(ob, oracle_lib):
+    """orc_count_overlaps (Collision.hpp:63-84 restated) against the reference's own
+    Collision::resolve: the pass leaves the world untouched exactly when no pair overlaps, and any
+    overlap merges at least the first pair (both bodies unpinned here)."""
+    if not ob.have_reference():
+        pytest.skip("oracle/_ref/libnbref.so not built")
+    rng = np.random.default_rng(11)
+    r = ob.Reference()
+    for radius in (0.0, 1e5, 6e5, 1e6, 2e6, 5e6):
+        n = 300
+        pos = (rng.standard_normal((n, 2)) * 1e8).astype(np.float32).astype(np.float64)
+        vel = (rng.standard_normal((n, 2)) * 1e3).astype(np.float32).astype(np.float64)
+        mass = rng.uniform(1e22, 1e24, n).astype(np.float32)
+        mass[3] = 0.0
+        pos[5, 1] = np.nan
+        rad = np.full(n, radius) * rng.uniform(0.5, 1.5, n)
+        cnt, first = oracle_lib.count_overlaps(pos, mass, rad)
+        r.load_bodies(pos, vel, mass)
+        left = r.collision_resolve(rad)
+        if cnt == 0:
+            assert left == n and first is None
+            p, v, _, m, _ = r.read_bodies()
+            assert np.array_equal(p, pos, equal_nan=True) and np.array_equal(v, vel) and np.array_equal(m, mass)
+        else:
+            assert left < n and first[0] < first[1] and 3 not in first and 5 not in first
+            _, _, _, m, _ = r.read_bodies()
+            merged = np.float32(np.float64(mass[first[0]]) + np.float64(mass[first[1]]))
+            assert merged in m or left < n - 1   # the first pair merged (its survivor may merge again later)
+    r.close()

@@ -7,7 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.ins
 import numpy as np
 import __graft_entry__ as ge
 pkg = ge.load_package(); sc = pkg.scenarios
-what = sys.argv[1:] or ["planar", "c3", "small"]
+what = sys.argv[1:] or ["planar", "c3", "small", "overlap"]
 
 def timed(ph, fn, reps=3):
     best = 1e30
@@ -53,3 +53,12 @@ if "small" in what:
             t2 = time.perf_counter(); ph.step(100.0, 200); ph.synchronize(); t3 = time.perf_counter()
             print(f"small: n={n} {name}: {(t1-t0)/200*1e6:.1f} us/frame one call per frame, {(t3-t2)/200*1e6:.1f} us/frame batched", flush=True)
             ph.close()
+if "overlap" in what:
+    for n in (65536, 1 << 20):
+        pos, vel, mass = sc.plummer(n, dim=2)
+        ph = pkg.Physics(0); ph.set_precision(pkg.PRECISION_FP32); ph.upload(pos, vel, mass)
+        rad = np.full(n, 1.0e3)
+        ph.count_overlaps(rad)
+        t0 = time.perf_counter(); got = ph.count_overlaps(rad); t1 = time.perf_counter()
+        print(f"overlap: n={n}: {1e3*(t1-t0):.2f} ms incl. radius upload, {n*(n-1)/2/(t1-t0):.3e} pairs/s, overlaps {got[0]}", flush=True)
+        ph.close()
