@@ -209,10 +209,11 @@ def run_ours(args):
             for h in (h_pos, h_vel, h_acc):
                 h[:] = pkg.sharded.gather_rows(dist, h, n)
     e2e_value = float(n) * n * e2e_steps / (e2e_ms * 1e-3)
-    h2d = n * (3 * 3 * 8 + 4)
+    h2d = (hi - lo) * (3 * 3 * 8 + 4 + 0)   # nb_upload_state copies a rank's own rows only (the rest arrive as FP32 sources over NVLink)
     d2h = (hi - lo) * 3 * 3 * 8
 
     general = None
+    planar = None
     if world == 1:
         # the same workload through the general-mass kernel (the production run above uses the
         # uniform-mass variant because every body of config 4 has the same mass)
@@ -230,6 +231,21 @@ def run_ours(args):
         pg.close()
         general = {"value": float(n) * n * 2 / (g_ms * 1e-3), "unit": UNIT, "steps": 2,
                    "note": "NB_FORCE_GENERIC=1: per-source masses multiplied in the kernel (12 instead of 11 FMA-pipe ops per pair)"}
+        # and the reference's own layout: the same sphere projected to z = 0 and uploaded as 2-D
+        # (Position/Velocity are DVec2), which selects the planar kernel variant
+        p2, v2, m2 = pkg.scenarios.plummer(n, seed=1234, dim=2)
+        pp = pkg.Physics(local_rank)
+        pp.set_precision(pkg.PRECISION_FP32)
+        pp.set_config(softening=eps, integrator=1)
+        pp.upload(p2, v2, m2)
+        pp.step(dt, 2)
+        pp.synchronize()
+        pp.timer_begin()
+        pp.step(dt, 2)
+        p_ms = pp.timer_end()
+        pp.close()
+        planar = {"value": float(n) * n * 2 / (p_ms * 1e-3), "unit": UNIT, "steps": 2,
+                  "note": "2-D reference layout (z = 0): 8 FMA-pipe ops per pair; counted as interactions, not as 20-FLOP work"}
 
     if rank == 0:
         props_sms = ph.device_info()["sm_count"]
@@ -269,7 +285,7 @@ def run_ours(args):
                        "l2": "flushed (256 MiB memset) before every timed step", "parallelism": f"target-partition x{world}"},
             "pct_fp32_peak": 100.0 * value * FLOPS_PER_INTERACTION / (peak * 1e12 * world),
             "steps_per_s": 1e3 * args.steps / total_ms,
-            "kernel_variant": "uniform-mass (all bodies of config 4 have equal mass)", "general_mass": general,
+            "kernel_variant": "uniform-mass (all bodies of config 4 have equal mass)", "general_mass": general, "planar_2d": planar,
             "roofline": roof, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,

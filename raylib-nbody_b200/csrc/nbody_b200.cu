@@ -210,16 +210,17 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
 // ---------------------------------------------------------------------------------------
 namespace {
 
-// staging: [pos dim*n doubles][vel dim*n doubles]; rows [0,n) of the SoA state
+// staging: [pos dim*rows doubles][vel ...][acc ...] for state rows [lo, lo + rows)
 __global__ void __launch_bounds__(256) unpack_aos_kernel(const double* pos, const double* vel, const double* acc,
-                                                         int dim, long long n, StateView s) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
+                                                         int dim, long long lo, long long rows, StateView s) {
+    const long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (q >= rows) return;
+    const long long i = lo + q;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        s.x[k][i] = k < dim ? pos[i * dim + k] : 0.0;
-        s.v[k][i] = k < dim ? vel[i * dim + k] : 0.0;
-        s.a[k][i] = (acc && k < dim) ? acc[i * dim + k] : 0.0;  // fresh entities: Acceleration{0}, Physics.hpp:97
+        s.x[k][i] = k < dim ? pos[q * dim + k] : 0.0;
+        s.v[k][i] = k < dim ? vel[q * dim + k] : 0.0;
+        s.a[k][i] = (acc && k < dim) ? acc[q * dim + k] : 0.0;  // fresh entities: Acceleration{0}, Physics.hpp:97
         s.a0[k][i] = 0.0;  // and PrevAcceleration{0}, :98
     }
 }
@@ -665,19 +666,27 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
     c->packed_valid = false;
     c->step_diag_valid = false;
     if (n == 0) return NB_OK;
-    const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n;
-    NB_TRY(ensure_staging(c, 3 * vec_bytes));
-    double* d_pos = static_cast<double*>(c->staging);
-    double* d_vel = d_pos + (size_t)dim * n;
-    double* d_acc = d_vel + (size_t)dim * n;
-    NB_CUDA(cudaMemcpyAsync(d_pos, pos, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(d_vel, vel, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-    if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(c->mass, mass, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
-    if (pinned) NB_CUDA(cudaMemcpyAsync(c->pinned, pinned, (size_t)n, cudaMemcpyHostToDevice, c->stream));
-    unpack_aos_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_pos, d_vel, acc ? d_acc : nullptr, dim, n, c->view());
-    NB_CUDA(cudaGetLastError());
-    c->kernel_launches++;
+    // a rank only needs the FP64 state of its own targets: the other bodies reach it as FP32 sources
+    // through the all-gather of the packed stream (prepare_packed), so only rows [lo,hi) are copied
+    const long long rows = c->hi - c->lo;
+    if (rows > 0) {
+        const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)rows;
+        const size_t off = (size_t)c->lo * dim;
+        NB_TRY(ensure_staging(c, 3 * vec_bytes));
+        double* d_pos = static_cast<double*>(c->staging);
+        double* d_vel = d_pos + (size_t)dim * rows;
+        double* d_acc = d_vel + (size_t)dim * rows;
+        NB_CUDA(cudaMemcpyAsync(d_pos, pos + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(d_vel, vel + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+        if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(c->mass + c->lo, mass + c->lo, sizeof(float) * rows, cudaMemcpyHostToDevice, c->stream));
+        if (pinned)
+            NB_CUDA(cudaMemcpyAsync(c->pinned + c->lo, pinned + c->lo, (size_t)rows, cudaMemcpyHostToDevice, c->stream));
+        unpack_aos_kernel<<<blocks_for(rows, 256), 256, 0, c->stream>>>(d_pos, d_vel, acc ? d_acc : nullptr, dim, c->lo,
+                                                                       rows, c->view());
+        NB_CUDA(cudaGetLastError());
+        c->kernel_launches++;
+    }
     c->acc_valid = acc != nullptr;
     NB_TRY(prepare_packed(c));
     // the borrowed host arrays may be pageable: do not return while a copy could still read them

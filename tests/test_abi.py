@@ -82,3 +82,21 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".sh")):
                 text = open(os.path.join(base, f)).read()
                 assert "oracle" not in text.lower().replace("oracle/", "oracle/") or f == "never", (base, f)
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py --impl reference runs on host cores only (the reference's own compute_gravity when
+    oracle/_ref is built, else the oracle port) and prints exactly one JSON line with the contract keys."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "1", "--ref-sample", "1024"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "interactions/s" and d["value"] > 0
+    assert d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["kind"] in ("reference", "port")
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]

@@ -55,3 +55,30 @@ def test_c4_full_size_properties(pkg):
     c = ph.counters()
     assert c["force_evals"] == 5 and c["interactions"] >= 5.0 * N * N
     ph.close()
+
+
+def test_c5_two_galaxy_collision_shape(pkg):
+    """Config 5's scenario (two Plummer spheres on a collision orbit, Velocity Verlet) at 2^16 bodies
+    on one GPU: energy conserved and total momentum constant over fused steps, third law at t = 0.
+    The 2^22-body, 8-GPU run is tools/config5.py (profiles/r01_config5_n8.jsonl)."""
+    n = 1 << 16
+    pos, vel, mass = pkg.scenarios.two_galaxies(n, seed=1234, dim=3)
+    eps = 3.844e8 / np.sqrt(n / 2)
+    dt = 1e-3 * pkg.scenarios.crossing_time(n // 2)
+    ph = pkg.Physics(0)
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(softening=eps, integrator=1)
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    acc = ph.download()[2]
+    m = mass.astype(np.float64)[:, None]
+    assert np.abs((m * acc).sum(axis=0)).max() <= 1e-6 * np.abs(m * acc).sum()
+    ph.step(dt, 1, diagnostics=True)
+    d0 = ph.step_diagnostics()
+    ph.step(dt, 20, diagnostics=True)
+    d1 = ph.step_diagnostics()
+    assert d0.ok and d1.ok
+    assert abs((d1.energy - d0.energy) / d0.energy) < 1e-6
+    pscale = float((m[:, 0] * np.linalg.norm(vel, axis=1)).sum())
+    assert np.abs(np.array(d1.momentum) - np.array(d0.momentum)).max() <= 1e-9 * pscale
+    ph.close()
