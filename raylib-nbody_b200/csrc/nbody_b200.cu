@@ -870,6 +870,22 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
     const double h = (double)dt_sub;
     const long long total = n_frames * (long long)n_steps;
     c->step_diag_exact = false;
+    if (use_exact(c) && c->n <= kSmallWorldMax) {
+        // the whole call in one launch (exact.cuh, small_world_steps_kernel)
+        const bool verlet = c->cfg.integrator != NB_INTEGRATOR_EULER;
+        const int first_force = verlet && !c->acc_valid ? 1 : 0;
+        const int threads = (int)std::max<long long>(32, ((c->n + 31) / 32) * 32);
+        small_world_steps_kernel<<<1, threads, 0, c->stream>>>(c->view(), c->cfg.g, c->cfg.softening, h, 0.5 * h * h,
+                                                              c->cfg.max_speed, verlet ? 1 : 0, first_force, total);
+        NB_CUDA(cudaGetLastError());
+        c->kernel_launches++;
+        c->force_evals += total + first_force;
+        c->interactions += (double)(total + first_force) * (double)c->n * (double)c->n;
+        c->acc_valid = verlet;  // Euler: Acceleration holds a(x) of the positions before the last move
+        c->packed_valid = false;
+        c->step_diag_exact = pot;
+        return NB_OK;
+    }
     if (use_exact(c)) {
         if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
             for (long long k = 0; k < total; ++k) {

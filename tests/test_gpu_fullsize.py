@@ -4,8 +4,12 @@ through size-independent properties, since the reference's O(N^2) FP64 loop need
   * a seeded subsample of targets against an FP64 direct sum over all 2^20 sources
     (numpy restatement of the oracle's pair term), tolerance 1e-5 per body;
   * energy conservation over fused Verlet steps from the fused potential."""
+import os
+
 import numpy as np
 import pytest
+
+from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
@@ -82,3 +86,27 @@ def test_c5_two_galaxy_collision_shape(pkg):
     pscale = float((m[:, 0] * np.linalg.norm(vel, axis=1)).sum())
     assert np.abs(np.array(d1.momentum) - np.array(d0.momentum)).max() <= 1e-9 * pscale
     ph.close()
+
+
+def test_c4_full_size_against_the_reference_itself(pkg):
+    """The 2^20-body sphere in the reference's own 2-D layout, against accelerations the UNMODIFIED
+    reference computed at full size (tests/golden/make_golden_fullsize.py: one compute_gravity pass,
+    ~40 min on one core; every 128th body committed). Runs the planar uniform-mass kernel."""
+    path = os.path.join(GOLDEN, "c4_plummer2d_2e20_subsample.npz")
+    if not os.path.exists(path):
+        pytest.skip("full-size fixture not generated")
+    g = np.load(path)
+    pos, vel, mass = pkg.scenarios.plummer(N, seed=1234, dim=2)
+    ph = pkg.Physics(0)
+    ph.set_precision(pkg.PRECISION_FP32)
+    ph.set_config(softening=float(g["softening"]))
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    acc = ph.download()[2]
+    ph.close()
+    idx = g["idx"]
+    err = np.linalg.norm(acc[idx] - g["acc"], axis=1) / np.linalg.norm(g["acc"], axis=1)
+    assert err.max() <= 1e-5, f"max rel err {err.max():.3e}"
+    assert np.median(err) <= 5e-7
+    m = mass.astype(np.float64)[:, None]
+    assert np.abs((m * acc).sum(axis=0) - g["net_force"]).max() <= 1e-6 * float(g["gross_force"])
