@@ -69,6 +69,9 @@ struct nb_ctx {
     float4* dpk = nullptr;              // stand-alone diagnostics pack
     void* l2_scratch = nullptr;         // 256 MiB, nb_flush_l2
     void* staging = nullptr;            // device staging for AoS uploads/downloads
+    void* collide_scratch = nullptr;    // nb_count_overlaps: radii, grid arrays, scan temp
+    size_t collide_bytes = 0;
+    long long overlap_grid_calls = 0;   // calls that took the O(N) grid broad phase
     size_t staging_bytes = 0;
 
     int gen = 0;               // generation of pk[gen & 1]

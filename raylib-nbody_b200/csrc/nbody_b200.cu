@@ -3,6 +3,7 @@
 // which force evaluations a frame needs, the substep plan, and when cached device state
 // (accelerations, the FP32 j-stream) is still valid. No CPU fallback exists in this file.
 #include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
 #include <dlfcn.h>
 #include <math.h>
 #include <stdio.h>
@@ -431,6 +432,7 @@ extern "C" void nb_destroy(nb_ctx* c) {
     free_bodies(c);
     cudaFree(c->extent);
     cudaFree(c->l2_scratch);
+    cudaFree(c->collide_scratch);
     cudaFree(c->totals);
     cudaFreeHost(c->h_totals);
     for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
@@ -1079,6 +1081,50 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
     return NB_OK;
 }
 
+namespace {
+
+int ensure_collide_scratch(nb_ctx* c, size_t bytes) {
+    if (bytes <= c->collide_bytes) return NB_OK;
+    if (c->collide_scratch) cudaFree(c->collide_scratch);
+    c->collide_scratch = nullptr;
+    c->collide_bytes = 0;
+    NB_CUDA(cudaMalloc(&c->collide_scratch, bytes));
+    c->collide_bytes = bytes;
+    return NB_OK;
+}
+
+inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+// Grid for the broad phase, or cells[0] == 0 when the all-pairs sweep is the better (or only) choice.
+GridSpec plan_grid(int dim, const double lo[3], const double hi[3], double r_max, long long n) {
+    GridSpec g{};
+    g.dim = dim;
+    double ext[3] = {hi[0] - lo[0], hi[1] - lo[1], dim == 3 ? hi[2] - lo[2] : 0.0};
+    const double ext_max = std::max(ext[0], std::max(ext[1], ext[2]));
+    if (!(ext_max > 0.0) || !std::isfinite(ext_max) || !(r_max >= 0.0) || !std::isfinite(r_max)) return g;
+    double h = 2.0 * r_max * (1.0 + 1e-9);
+    h = std::max(h, ext_max * 9.5367431640625e-07);  // at most 2^20 cells per axis
+    const double cap = (double)std::max<long long>(4 * n, 1 << 16);
+    for (int it = 0; it < 8; ++it) {
+        double prod = 1.0;
+        for (int k = 0; k < dim; ++k) prod *= std::floor(ext[k] / h) + 1.0;
+        if (prod <= cap) break;
+        h *= std::pow(prod / cap, 1.0 / dim) * 1.01;
+    }
+    long long prod = 1;
+    for (int k = 0; k < 3; ++k) {
+        g.cells[k] = k < dim ? (int)std::floor(ext[k] / h) + 1 : 1;
+        g.origin[k] = lo[k];
+        prod *= g.cells[k];
+    }
+    g.inv_h = 1.0 / h;
+    // a neighbourhood that covers most of the world is an all-pairs sweep with extra steps
+    if ((double)prod > cap * 1.05 || std::max(g.cells[0], g.cells[1]) < 8) g.cells[0] = 0;
+    return g;
+}
+
+}  // namespace
+
 extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair) {
     if (!c || !n_overlaps) return fail(NB_ERR_INVALID, "nb_count_overlaps: null");
     if (c->world > 1) return fail(NB_ERR_INVALID, "nb_count_overlaps: single-GPU contexts only (FP64 positions are not replicated)");
@@ -1087,29 +1133,87 @@ extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_ove
     if (c->n < 2) return NB_OK;  // Collision.hpp:70
     if (!radius) return fail(NB_ERR_INVALID, "nb_count_overlaps: null radius array");
     NB_CUDA(cudaSetDevice(c->device));
-    const size_t r_bytes = sizeof(double) * (size_t)c->n;
-    NB_TRY(ensure_staging(c, r_bytes + 16));
-    double* d_radius = static_cast<double*>(c->staging);
-    unsigned long long* d_res = reinterpret_cast<unsigned long long*>(static_cast<char*>(c->staging) + r_bytes);
-    const unsigned long long init[2] = {0ull, ~0ull};
-    NB_CUDA(cudaMemcpyAsync(d_radius, radius, r_bytes, cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(d_res, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
+    const long long n = c->n;
     const StateView s = c->view();
-    if (c->dim == 2)
-        overlap_kernel<true><<<blocks_for(c->n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-            s.x[0], s.x[1], s.x[2], c->mass, d_radius, c->n, d_res);
-    else
-        overlap_kernel<false><<<blocks_for(c->n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-            s.x[0], s.x[1], s.x[2], c->mass, d_radius, c->n, d_res);
+    double r_max = 0.0;
+    for (long long i = 0; i < n; ++i) r_max = std::fabs(radius[i]) > r_max || std::isnan(radius[i]) ? std::fabs(radius[i]) : r_max;
+    const char* mode = getenv("NB_OVERLAP_MODE");  // developer/test knob: "pairs" or "grid"
+    const bool want_grid = !(mode && !strcmp(mode, "pairs")) && (n >= 2048 || (mode && !strcmp(mode, "grid")));
+
+    // scratch layout: header (bounds[6], result[2]) | radius | grid arrays
+    const size_t off_radius = 256, off_grid = off_radius + align256(sizeof(double) * (size_t)n);
+    NB_TRY(ensure_collide_scratch(c, off_grid));
+    char* base = static_cast<char*>(c->collide_scratch);
+    unsigned long long* d_bounds = reinterpret_cast<unsigned long long*>(base);
+    unsigned long long* d_res = d_bounds + 6;
+    double* d_radius = reinterpret_cast<double*>(base + off_radius);
+    const unsigned long long init[8] = {~0ull, 0ull, ~0ull, 0ull, ~0ull, 0ull, 0ull, ~0ull};
+    NB_CUDA(cudaMemcpyAsync(d_bounds, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(d_radius, radius, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+
+    GridSpec g{};
+    if (want_grid) {
+        const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n, 256), 4 * c->sm_count);
+        collide_bounds_kernel<<<grid, 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, d_bounds);
+        c->kernel_launches++;
+        unsigned long long hb[6];
+        NB_CUDA(cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (hb[0] <= hb[1]) {  // at least one body passed the filter
+            double lo[3], hi[3];
+            for (int k = 0; k < 3; ++k) { lo[k] = dbl_from_order_key(hb[2 * k]); hi[k] = dbl_from_order_key(hb[2 * k + 1]); }
+            g = plan_grid(c->dim, lo, hi, r_max, n);
+        }
+    }
+    if (g.cells[0] > 0) {
+        const size_t n_cells = (size_t)g.cells[0] * g.cells[1] * g.cells[2];
+        size_t cub_bytes = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, cub_bytes, (unsigned int*)nullptr, (unsigned int*)nullptr, (int)(n_cells + 1), c->stream);
+        const size_t off_count = off_grid, off_start = off_count + align256(4 * (n_cells + 1)),
+                     off_fill = off_start + align256(4 * (n_cells + 1)), off_sorted = off_fill + align256(4 * n_cells),
+                     off_cub = off_sorted + align256(4 * (size_t)n), total = off_cub + align256(cub_bytes);
+        if (total > c->collide_bytes) {  // growing frees the old block: re-stage the header and radii
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            NB_TRY(ensure_collide_scratch(c, total));
+            base = static_cast<char*>(c->collide_scratch);
+            d_bounds = reinterpret_cast<unsigned long long*>(base);
+            d_res = d_bounds + 6;
+            d_radius = reinterpret_cast<double*>(base + off_radius);
+            NB_CUDA(cudaMemcpyAsync(d_bounds, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
+            NB_CUDA(cudaMemcpyAsync(d_radius, radius, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        }
+        unsigned int* cell_count = reinterpret_cast<unsigned int*>(base + off_count);
+        unsigned int* cell_start = reinterpret_cast<unsigned int*>(base + off_start);
+        unsigned int* cell_fill = reinterpret_cast<unsigned int*>(base + off_fill);
+        unsigned int* sorted_idx = reinterpret_cast<unsigned int*>(base + off_sorted);
+        NB_CUDA(cudaMemsetAsync(cell_count, 0, 4 * (n_cells + 1), c->stream));
+        NB_CUDA(cudaMemsetAsync(cell_fill, 0, 4 * n_cells, c->stream));
+        grid_bin_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, g, cell_count, nullptr,
+                                                                  nullptr, nullptr);
+        NB_CUDA(cub::DeviceScan::ExclusiveSum(base + off_cub, cub_bytes, cell_count, cell_start, (int)(n_cells + 1), c->stream));
+        grid_bin_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, g, nullptr, cell_start,
+                                                                  cell_fill, sorted_idx);
+        grid_overlap_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, g,
+                                                                      cell_start, sorted_idx, d_res);
+        c->kernel_launches += 4;
+        c->overlap_grid_calls++;
+    } else {
+        if (c->dim == 2)
+            overlap_kernel<true><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
+                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res);
+        else
+            overlap_kernel<false><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
+                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res);
+        c->kernel_launches++;
+    }
     NB_CUDA(cudaGetLastError());
-    c->kernel_launches++;
     unsigned long long res[2];
     NB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     *n_overlaps = (int64_t)res[0];
     if (first_pair && res[0]) {
-        first_pair[0] = (int64_t)(res[1] / (unsigned long long)c->n);
-        first_pair[1] = (int64_t)(res[1] % (unsigned long long)c->n);
+        first_pair[0] = (int64_t)(res[1] / (unsigned long long)n);
+        first_pair[1] = (int64_t)(res[1] % (unsigned long long)n);
     }
     return NB_OK;
 }

@@ -403,11 +403,13 @@ def test_specialised_kernels_match_oracle_and_generic(pkg, oracle_lib, ob, dim, 
 
 
 # ---- collision detection (detection phase) --------------------------------
+@pytest.mark.parametrize("mode", ["pairs", "grid"])
 @pytest.mark.parametrize("n", [2, 257, 1000, 5000])
-def test_overlap_detection_matches_oracle(pkg, ph, oracle_lib, n):
+def test_overlap_detection_matches_oracle(pkg, ph, oracle_lib, n, mode, monkeypatch):
     """nb_count_overlaps == the oracle's restatement of Collision.hpp:63-84, bit-exact decisions:
     same count and same first pair, with filtered bodies, huge and zero radii, and pairs placed
     exactly on the dist2 == rsum^2 boundary (which the reference counts as overlapping)."""
+    monkeypatch.setenv("NB_OVERLAP_MODE", mode)   # all-pairs sweep / uniform-grid broad phase
     rng = np.random.default_rng(n)
     pos = (rng.standard_normal((n, 2)) * 1e8).astype(np.float32).astype(np.float64)
     vel = np.zeros((n, 2))
@@ -436,6 +438,25 @@ def test_overlap_detection_matches_oracle(pkg, ph, oracle_lib, n):
         rad[9] = 2.4999e6                                                              # just inside: no longer
         got = ph.count_overlaps(rad)
         assert got == oracle_lib.count_overlaps(pos, mass, rad) and got[1] != (8, 9)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_overlap_grid_equals_all_pairs_large(pkg, ph, dim, monkeypatch):
+    """40 000 clustered bodies (Plummer sphere, 10:1 radius spread): the O(N) grid broad phase and the
+    all-pairs sweep return the same count and the same first pair, in 2-D and 3-D."""
+    n = 40000
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=3, dim=dim)
+    rng = np.random.default_rng(9)
+    rad = 1.5e6 * rng.uniform(0.2, 2.0, n)
+    ph.upload(pos, vel, mass)
+    monkeypatch.setenv("NB_OVERLAP_MODE", "pairs")
+    a = ph.count_overlaps(rad)
+    monkeypatch.setenv("NB_OVERLAP_MODE", "grid")
+    b = ph.count_overlaps(rad)
+    monkeypatch.delenv("NB_OVERLAP_MODE")
+    c = ph.count_overlaps(rad)   # automatic choice
+    assert a == b == c and a[0] > 0
+    assert ph.count_overlaps(np.zeros(n)) == (0, None)
 
 
 # ---- edge cases -------------------------------------------------------------------------------
