@@ -66,6 +66,11 @@ public:
         bool config_applied = false;
         long long uploads = 0, frames = 0;
         long long collision_checks = 0, collision_frames = 0;  // device detections / frames that ran the CPU merge
+        // Verlet: the kick pass of frame k also accumulates the potential at the positions frame k+1 starts
+        // from, so its fused diagnostics ARE frame k+1's frame-start diagnostics unless something was edited
+        bool diag_cached = false;
+        nb_diag cached_diag{};
+        long long diag_reused = 0;
     };
 
     static void check(int status, const char* what) {
@@ -103,6 +108,7 @@ public:
 
     static void apply_config(Device& d, const Config& cfg) {
         nb_config c;
+        std::memset(&c, 0, sizeof(c));  // padding too: the struct is compared bytewise below
         c.g = cfg.g;
         c.softening = cfg.softening;
         c.max_speed = cfg.max_speed;
@@ -111,6 +117,7 @@ public:
         c.max_substeps_per_frame = cfg.max_substeps_per_frame;
         if (d.config_applied && std::memcmp(&c, &d.applied, sizeof(c)) == 0) return;
         check(nb_set_config(d.ctx, &c), "nb_set_config");
+        d.diag_cached = false;
         d.applied = c;
         d.config_applied = true;
     }
@@ -127,6 +134,7 @@ public:
             d.uploads++;
             d.mirror = now;
             d.resident = true;
+            d.diag_cached = false;
         }
         return now;
     }
@@ -147,7 +155,12 @@ public:
         apply_config(d, *cfg);
         sync(w, d);
         nb_diag r;
-        check(nb_compute_diagnostics(d.ctx, &r), "nb_compute_diagnostics");
+        if (d.diag_cached) {
+            r = d.cached_diag;
+            d.diag_reused++;
+        } else {
+            check(nb_compute_diagnostics(d.ctx, &r), "nb_compute_diagnostics");
+        }
         if (!r.ok) {  // Physics.hpp:140-145,155-159,170-175: auto-pause, zeroed struct
             cfg->paused = true;
             out.ok = false;
@@ -184,6 +197,7 @@ public:
                               b.pinned.data()),
               "nb_upload_state");
         d.uploads++;
+        d.diag_cached = false;
         check(nb_integrate(d.ctx, dt), "nb_integrate");
         const bool verlet = cfg.integrator != 0;
         pull(d, b, verlet);
@@ -196,6 +210,7 @@ public:
     static void zero_net_momentum(const flecs::world& w, Device& d) {
         Bodies b = sync(w, d);
         if (b.size() == 0) return;
+        d.diag_cached = false;
         check(nb_zero_net_momentum(d.ctx), "nb_zero_net_momentum");
         pull(d, b, false);
         scatter(w, b, 1);
@@ -252,8 +267,15 @@ public:
             const float dtEff = baseDt * std::max(0.0f, cfg.time_scale);  // Physics.hpp:54-55
             Bodies b = sync(w, dev);  // merges flushed at the end of sysA show up here as an edit
             if (b.size() == 0) return;
-            check(nb_step(dev.ctx, dtEff, 1), "nb_step");
             const bool verlet = cfg.integrator != 0;
+            dev.diag_cached = false;
+            if (verlet) {
+                check(nb_step_with_diagnostics(dev.ctx, dtEff, 1), "nb_step_with_diagnostics");
+                check(nb_step_diagnostics(dev.ctx, &dev.cached_diag), "nb_step_diagnostics");
+                dev.diag_cached = true;
+            } else {
+                check(nb_step(dev.ctx, dtEff, 1), "nb_step");
+            }
             pull(dev, b, verlet);
             scatter(w, b, verlet ? 7 : 3);
             dev.mirror = b;

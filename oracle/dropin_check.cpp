@@ -182,8 +182,10 @@ int main() {
         expect(dr && db && dr->ok && db->ok && std::fabs(dr->energy - db->energy) <= 2e-6 * std::fabs(dr->energy),
                "Diagnostics energy within 2e-6");
         const auto* dev = wb.get<PhysicsB200::Device>();
-        std::printf("  uploads %lld over %lld frames\n", dev->uploads, dev->frames);
+        std::printf("  uploads %lld over %lld frames, frame-start diagnostics taken from the previous step %lld times\n",
+                    dev->uploads, dev->frames, dev->diag_reused);
         expect(dev->uploads == 2, "one upload at start, one after the external edit, none otherwise");
+        expect(dev->diag_reused == 6, "Verlet frames after the first / after the edit reuse the fused diagnostics (4 + 2)");
 
         // non-finite body: the reference pauses itself (Physics.hpp:140-145); so must the binding
         for (flecs::world* w : {&wr, &wb}) {

@@ -62,3 +62,13 @@ if "overlap" in what:
         t0 = time.perf_counter(); got = ph.count_overlaps(rad); t1 = time.perf_counter()
         print(f"overlap: n={n}: {1e3*(t1-t0):.2f} ms incl. radius upload, {n*(n-1)/2/(t1-t0):.3e} pairs/s, overlaps {got[0]}", flush=True)
         ph.close()
+if "diag" in what:
+    for n in (65536, 1 << 20):
+        pos, vel, mass = sc.plummer(n, dim=3); eps = 3.844e8 / np.sqrt(n); dt = 1e-3 * sc.crossing_time(n)
+        ph = pkg.Physics(0); ph.set_precision(pkg.PRECISION_FP32); ph.set_config(softening=eps); ph.upload(pos, vel, mass)
+        ph.compute_diagnostics()
+        t0 = time.perf_counter(); d = ph.compute_diagnostics(); t1 = time.perf_counter()
+        ph.step(dt, 1, diagnostics=True); ph.synchronize()
+        t2 = time.perf_counter(); ph.step(dt, 1, diagnostics=True); d2 = ph.step_diagnostics(); t3 = time.perf_counter()
+        print(f"diag: n={n}: stand-alone compute_diagnostics {1e3*(t1-t0):.2f} ms; step with fused diagnostics {1e3*(t3-t2):.2f} ms", flush=True)
+        ph.close()
