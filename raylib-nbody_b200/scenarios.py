@@ -96,3 +96,38 @@ def two_galaxies(n, seed=1234, scale=EARTH_MOON, g=G_DEFAULT, dim=3):
 def crossing_time(n, scale=EARTH_MOON, mass=MOON_MASS, g=G_DEFAULT):
     """sqrt(a^3 / (G M)) of a Plummer sphere of n bodies: the natural time unit for dt."""
     return float(np.sqrt(scale ** 3 / (g * mass * n)))
+
+
+# ---- scenario snapshots --------------------------------------------------------------------------
+# The reference keeps scenarios in memory only (src/core/Scenario.hpp:14-50: bodies + a Config
+# subset, nothing on disk). Same content here, as one .npz, so a device run can be checkpointed
+# (Physics.download_state) and resumed (Physics.upload_state) bit for bit.
+SNAPSHOT_CONFIG_KEYS = ("g", "softening", "max_speed", "integrator", "max_substep", "max_substeps_per_frame")
+
+
+def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, config=None, frame=0):
+    """Bodies (Scenario::BodyData, Scenario.hpp:14-21) plus the physics Config fields."""
+    n = len(mass)
+    data = {"pos": np.asarray(pos, np.float64), "vel": np.asarray(vel, np.float64),
+            "mass": np.asarray(mass, np.float32),
+            "pinned": np.zeros(n, np.uint8) if pinned is None else np.asarray(pinned, np.uint8),
+            "frame": np.int64(frame)}
+    if acc is not None:
+        data["acc"] = np.asarray(acc, np.float64)
+    if acc_prev is not None:
+        data["acc_prev"] = np.asarray(acc_prev, np.float64)
+    for k, v in (config or {}).items():
+        if k not in SNAPSHOT_CONFIG_KEYS:
+            raise KeyError(f"not a physics Config field: {k}")
+        data["cfg_" + k] = np.float64(v)
+    np.savez_compressed(path, **data)
+
+
+def load_snapshot(path):
+    """-> dict(pos, vel, mass, pinned, acc|None, acc_prev|None, config, frame); floats round-trip exactly."""
+    z = np.load(path)
+    cfg = {k: (int(z["cfg_" + k]) if k in ("integrator", "max_substeps_per_frame") else float(z["cfg_" + k]))
+           for k in SNAPSHOT_CONFIG_KEYS if "cfg_" + k in z.files}
+    return {"pos": z["pos"], "vel": z["vel"], "mass": z["mass"], "pinned": z["pinned"],
+            "acc": z["acc"] if "acc" in z.files else None, "acc_prev": z["acc_prev"] if "acc_prev" in z.files else None,
+            "config": cfg, "frame": int(z["frame"])}

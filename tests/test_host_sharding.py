@@ -53,3 +53,23 @@ def test_two_rank_gloo_plumbing(pkg, tmp_path, n):
     mp.spawn(_worker, args=(2, port, n, str(tmp_path)), nprocs=2, join=True)
     spans = [np.load(tmp_path / f"ok{r}.npy") for r in range(2)]
     assert spans[0][0] == 0 and spans[0][1] == spans[1][0] and spans[1][1] == n
+
+
+def test_snapshot_round_trip_is_bit_exact(pkg, tmp_path):
+    """Scenario snapshots (Scenario.hpp:14-50 content, on disk): every float comes back bit for bit."""
+    sc = pkg.scenarios
+    pos, vel, mass = sc.uniform_disk(500, seed=4, circular=True)
+    pos[3, 0] = np.nan
+    vel[4, 1] = -0.0
+    pinned = (np.arange(500) % 7 == 0).astype(np.uint8)
+    acc = np.random.default_rng(1).standard_normal(pos.shape)
+    cfg = {"g": 6.6743e-11, "softening": 4.0, "integrator": 1, "max_substep": 1e9}
+    path = str(tmp_path / "snap.npz")
+    sc.save_snapshot(path, pos, vel, mass, pinned, acc=acc, config=cfg, frame=123)
+    s = sc.load_snapshot(path)
+    assert s["pos"].tobytes() == pos.tobytes() and s["vel"].tobytes() == vel.tobytes()
+    assert s["mass"].tobytes() == mass.tobytes() and np.array_equal(s["pinned"], pinned)
+    assert s["acc"].tobytes() == acc.tobytes() and s["acc_prev"] is None
+    assert s["config"] == cfg and s["frame"] == 123
+    with pytest.raises(KeyError):
+        sc.save_snapshot(path, pos, vel, mass, config={"bh_theta": 0.5})
