@@ -7,6 +7,7 @@
 // same world.progress() calls, same external edits; the components are compared afterwards.
 // Built by oracle/Makefile into oracle/_ref/dropin_check (needs the reference's headers).
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cmath>
 #include <cstdint>
@@ -223,6 +224,31 @@ int main() {
         expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel) && bitwise(r.acc, b.acc), "state bit-identical after merges");
         expect(dev->collision_checks == 40 && dev->collision_frames >= 1 && dev->collision_frames < 40,
                "the reference's O(N^2) collision pass ran only on the frames with an overlap");
+        PhysicsB200::shutdown(wb);
+    }
+    // ---- D: what the drop-in buys per frame (whole world.progress(): collisions, diagnostics, gravity,
+    //         integrate, gather/scatter), 16 384 bodies with physical radii, Velocity Verlet ------------
+    {
+        flecs::world wr, wb;
+        make_config(wr, 1);
+        make_config(wb, 1);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0);
+        add_disk(wr, 16384, 5, 2.0e6f, false);
+        add_disk(wb, 16384, 5, 2.0e6f, false);
+        for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->time_scale = 3.0e4f;
+        const float dt = wr.get<Config>()->fixed_dt;
+        auto seconds = [&](flecs::world& w, int frames) {
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int f = 0; f < frames; ++f) w.progress(dt);
+            return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / frames;
+        };
+        wb.progress(dt);  // first frame uploads
+        wr.progress(dt);
+        const double tr = seconds(wr, 2), tb = seconds(wb, 20);
+        const Snapshot r = snap(wr), b = snap(wb);
+        std::printf("16384-body frame (flecs world.progress, Verlet): reference %.3f s, binding %.6f s  (x%.0f)\n", tr, tb, tr / tb);
+        expect(tb < tr, "the binding's frame is faster than the reference's");
         PhysicsB200::shutdown(wb);
     }
     std::printf(failures ? "DROPIN CHECK FAILED (%d)\n" : "DROPIN CHECK PASSED\n", failures);
