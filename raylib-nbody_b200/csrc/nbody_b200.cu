@@ -187,10 +187,13 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
         for (int nseg = 1; nseg <= seg_hi; ++nseg) {
             if (c->forced_nseg && nseg != c->forced_nseg && !(c->forced_nseg > seg_hi && nseg == seg_hi)) continue;
             const long long units = n_it * nseg;
-            const long long waves = (units + slots - 1) / slots;
-            double eff = (double)units / (double)(waves * slots);
+            // CTAs do not run in lock-step waves: the launch takes (work / slots) plus a tail of about a
+            // tenth of one CTA's duration (measured at N = 2^20: 2 -> 13 segments gains 1.3 %,
+            // profiles/r01_time_modes.txt), or (work / units) when the grid cannot fill the slots
+            const double per_unit = (double)slots / (double)units;
+            const double eff = 1.0 / (std::max(1.0, per_unit) + 0.1 * per_unit);
             // larger R amortises shared-memory reads; each extra segment costs a partial round-trip
-            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.002 * (nseg - 1));
+            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.0002 * (nseg - 1));
             if (score > best_score) {
                 best_score = score;
                 best.variant = (int)(ke - kKernels);
