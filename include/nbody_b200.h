@@ -42,8 +42,8 @@ typedef enum nb_status {
 typedef struct nb_ctx nb_ctx;
 
 /* Physics fields of the reference's Config singleton (src/core/Config.hpp:13-29,
- * defaults src/core/Constants.hpp:86-100). bh_threshold/bh_theta are absent on purpose:
- * this library always evaluates the direct sum (Physics.hpp:231-258). */
+ * defaults src/core/Constants.hpp:86-100). bh_threshold/bh_theta are set with nb_set_solver:
+ * by default this library always evaluates the direct sum (Physics.hpp:231-258). */
 typedef struct nb_config {
     double g;                   /* Config::g                      6.6743e-11 */
     float softening;            /* Config::softening (epsilon, m) 4.0        */
@@ -65,6 +65,21 @@ typedef struct nb_config {
 #define NB_PRECISION_FP32 1
 #define NB_PRECISION_FP64_EXACT 2
 #define NB_EXACT_AUTO_MAX 512
+
+/* Which branch of Physics::compute_gravity runs (nb_set_solver).
+ *   DIRECT     always the all-pairs sum (Physics.hpp:231-258) — the reference's behaviour when
+ *              n <= bh_threshold, and this library's hot path at every size. Default.
+ *   REFERENCE  the reference's own switch (Physics.hpp:212): a world with more than bh_threshold
+ *              bodies passing the gather filter is evaluated with the reference's float
+ *              Barnes-Hut quadtree (src/physics/SpatialPartition.hpp:36-220, opening angle
+ *              bh_theta), reproduced bit for bit on the device together with the FP64 integrator
+ *              arithmetic, so whole trajectories equal the reference's at its DEFAULT settings
+ *              (bh_threshold = 100, bh_theta = 0.5: Constants.hpp:90-91). Smaller worlds take the
+ *              direct sum as under DIRECT. 2-D uploads, single-GPU contexts. Two bodies whose
+ *              float coordinates coincide make the reference subdivide without end; here the
+ *              force evaluation returns NB_ERR_INVALID instead. */
+#define NB_SOLVER_DIRECT 0
+#define NB_SOLVER_REFERENCE 1
 
 #define NB_INTEGRATOR_EULER 0
 #define NB_INTEGRATOR_VERLET 1
@@ -104,6 +119,14 @@ int nb_default_config(nb_config* out);            /* Constants.hpp:86-100 + Conf
 int nb_set_config(nb_ctx* ctx, const nb_config* cfg);
 int nb_get_config(nb_ctx* ctx, nb_config* out);
 int nb_set_precision(nb_ctx* ctx, int precision); /* NB_PRECISION_*; single-GPU contexts only for FP64_EXACT */
+/* Config::bh_threshold / Config::bh_theta (Config.hpp:17-18) and whether to honour them. */
+int nb_set_solver(nb_ctx* ctx, int solver, int32_t bh_threshold, float bh_theta);
+int nb_get_solver(nb_ctx* ctx, int* solver, int32_t* bh_threshold, float* bh_theta);
+/* Tree of the last Barnes-Hut pass: values[8] = passes so far, cells, deepest level, bodies in the
+ * tree, and — counted only after nb_solver_profile(ctx, 1) — cells visited, terms added and accept
+ * tests re-evaluated in FP64 by the walks of the last pass; values[7] = 0. Synchronises. */
+int nb_solver_info(nb_ctx* ctx, int64_t* values);
+int nb_solver_profile(nb_ctx* ctx, int enable);
 
 /* ---- state ------------------------------------------------------------------------ */
 

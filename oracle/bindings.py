@@ -35,19 +35,27 @@ def _b(a):
 
 class OrcConfig(C.Structure):
     _fields_ = [("g", C.c_double), ("softening", C.c_float), ("max_speed", C.c_float),
-                ("integrator", C.c_int), ("max_substep", C.c_float), ("max_substeps_per_frame", C.c_int)]
+                ("integrator", C.c_int), ("max_substep", C.c_float), ("max_substeps_per_frame", C.c_int),
+                ("bh_threshold", C.c_int), ("bh_theta", C.c_float)]
 
 
 # Reference defaults (src/core/Constants.hpp:86-100, src/core/Config.hpp:25).
 DEFAULTS = dict(g=6.67430e-11, softening=4.0, max_speed=0.0, integrator=1, fixed_dt=float(np.float32(1.0) / np.float32(120)),
                 time_scale=1e6, max_substep=1.0e9, max_substeps_per_frame=200)
+# Solver switch (Config.hpp:17-18). The reference's own defaults are REF_BH_THRESHOLD / REF_BH_THETA
+# (Constants.hpp:90-91); the checkers default to "never" so the direct sum — the north-star path — is
+# what a test gets unless it asks for the tree.
+BH_NEVER = 2**31 - 1
+REF_BH_THRESHOLD = 100
+REF_BH_THETA = 0.5
+DEFAULTS.update(bh_threshold=BH_NEVER, bh_theta=REF_BH_THETA)
 
 
 def make_config(**kw):
     d = dict(DEFAULTS)
     d.update(kw)
     return OrcConfig(d["g"], d["softening"], d["max_speed"], d["integrator"], d["max_substep"],
-                     d["max_substeps_per_frame"])
+                     d["max_substeps_per_frame"], d["bh_threshold"], d["bh_theta"])
 
 
 def dt_eff(fixed_dt=DEFAULTS["fixed_dt"], time_scale=DEFAULTS["time_scale"]):
@@ -80,6 +88,22 @@ class Oracle:
         fn = self.lib.orc_compute_gravity if dim == 2 else self.lib.orc_compute_gravity3
         fn(C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned), C.c_double(g), C.c_float(softening), _d(acc))
         return acc
+
+    def bh_gravity(self, pos, vel, mass, pinned=None, g=DEFAULTS["g"], softening=DEFAULTS["softening"],
+                   theta=REF_BH_THETA, acc=None, with_stats=False):
+        """Barnes-Hut branch of compute_gravity (Physics.hpp:212-230), 2-D. Raises if two gathered bodies
+        share their float coordinates (the reference does not terminate on such input)."""
+        n = pos.shape[0]
+        out = np.zeros((n, 2), np.float64) if acc is None else acc
+        stats = np.zeros(4, np.int64)
+        self.lib.orc_bh_gravity.restype = C.c_int64
+        rc = self.lib.orc_bh_gravity(C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned), C.c_double(g),
+                                     C.c_float(softening), C.c_float(theta), _d(out),
+                                     stats.ctypes.data_as(C.POINTER(C.c_int64)))
+        if rc < 0:
+            raise ValueError("coincident float positions: the reference's quadtree does not terminate")
+        return (out, dict(nodes=int(stats[0]), depth=int(stats[1]), popped=int(stats[2]), terms=int(stats[3]))) \
+            if with_stats else out
 
     def substep_plan(self, dt, max_substep=DEFAULTS["max_substep"], max_substeps=DEFAULTS["max_substeps_per_frame"]):
         out = C.c_float()
@@ -157,6 +181,14 @@ class Reference:
         self.lib.ref_set_config(self.h, C.c_double(d["g"]), C.c_float(d["softening"]), C.c_float(d["max_speed"]),
                                 C.c_int(d["integrator"]), C.c_float(d["fixed_dt"]), C.c_float(d["time_scale"]),
                                 C.c_float(d["max_substep"]), C.c_int(d["max_substeps_per_frame"]))
+
+    def set_solver(self, bh_threshold=REF_BH_THRESHOLD, bh_theta=REF_BH_THETA):
+        self.lib.ref_set_solver(self.h, C.c_int(int(bh_threshold)), C.c_float(bh_theta))
+
+    def solver_defaults(self):
+        t, th = C.c_int(), C.c_float()
+        self.lib.ref_get_solver_defaults(C.byref(t), C.byref(th))
+        return t.value, th.value
 
     def defaults(self):
         g = C.c_double()

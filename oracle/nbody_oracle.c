@@ -28,6 +28,8 @@ typedef struct {
     int integrator;             /* Config.hpp:25, 0 = semi-implicit Euler, 1 = velocity Verlet */
     float max_substep;          /* Config.hpp:28 */
     int max_substeps_per_frame; /* Config.hpp:29 */
+    int bh_threshold;           /* Config.hpp:17: Barnes-Hut above this many gathered bodies (2-D only) */
+    float bh_theta;             /* Config.hpp:18 */
 } orc_config;
 
 static int body_is_live(const double* p, const double* v, float m, int dim) {
@@ -87,6 +89,30 @@ void orc_compute_gravity3(int64_t n, const double* pos, const double* vel, const
     gravity_dim(n, pos, vel, mass, pinned, g, softening, acc, 3);
 }
 
+/* Barnes-Hut branch of compute_gravity (oracle/bh_oracle.c). */
+int64_t orc_bh_gravity(int64_t n, const double* pos, const double* vel, const float* mass, const uint8_t* pinned,
+                       double g, float softening, float theta, double* acc, int64_t* stats);
+
+/* The switch of Physics.hpp:212: the quadtree when more than bh_threshold bodies pass the gather
+ * filter, the direct sum otherwise. The 3-D extension has no tree (the reference is 2-D). */
+static void gravity_switch(int64_t n, const double* pos, const double* vel, const float* mass,
+                           const uint8_t* pinned, const orc_config* cfg, double* acc, int dim) {
+    if (dim == 2) {
+        int64_t live = 0;
+        for (int64_t i = 0; i < n; ++i) live += body_is_live(pos + 2 * i, vel + 2 * i, mass[i], 2);
+        if (live > (int64_t)cfg->bh_threshold) {
+            orc_bh_gravity(n, pos, vel, mass, pinned, cfg->g, cfg->softening, cfg->bh_theta, acc, NULL);
+            return;
+        }
+    }
+    gravity_dim(n, pos, vel, mass, pinned, cfg->g, cfg->softening, acc, dim);
+}
+
+void orc_compute_gravity_cfg(int64_t n, const double* pos, const double* vel, const float* mass,
+                             const uint8_t* pinned, const orc_config* cfg, double* acc) {
+    gravity_switch(n, pos, vel, mass, pinned, cfg, acc, 2);
+}
+
 /* Substep plan, Physics.hpp:268-271 (float arithmetic throughout). */
 int orc_substep_plan(float dt, float max_substep, int max_substeps_per_frame, float* dt_sub) {
     const float cap = fmaxf(1e-6f, max_substep);
@@ -127,7 +153,7 @@ static void integrate_dim(int64_t n, double* pos, double* vel, double* acc, doub
                 for (int k = 0; k < dim; ++k) pos[dim * i + k] += vel[dim * i + k] * h; /* :288 */
             }
             if (step + 1 < n_steps) /* :292 */
-                gravity_dim(n, pos, vel, mass, pinned, cfg->g, cfg->softening, acc, dim);
+                gravity_switch(n, pos, vel, mass, pinned, cfg, acc, dim);
         }
     } else {
         const double half_dt2 = 0.5 * h * h; /* :300 */
@@ -139,7 +165,7 @@ static void integrate_dim(int64_t n, double* pos, double* vel, double* acc, doub
                     acc_prev[dim * i + k] = acc[dim * i + k];                               /* :303 */
                 }
             }
-            gravity_dim(n, pos, vel, mass, pinned, cfg->g, cfg->softening, acc, dim); /* :307 */
+            gravity_switch(n, pos, vel, mass, pinned, cfg, acc, dim); /* :307 */
             for (int64_t i = 0; i < n; ++i) {
                 if (pinned && pinned[i]) continue;
                 for (int k = 0; k < dim; ++k) {
@@ -167,7 +193,7 @@ void orc_physics_frames(int64_t n, double* pos, double* vel, double* acc, double
                         const float* mass, const uint8_t* pinned, const orc_config* cfg, float dt_eff,
                         int64_t n_frames) {
     for (int64_t f = 0; f < n_frames; ++f) {
-        gravity_dim(n, pos, vel, mass, pinned, cfg->g, cfg->softening, acc, 2);
+        gravity_switch(n, pos, vel, mass, pinned, cfg, acc, 2);
         integrate_dim(n, pos, vel, acc, acc_prev, mass, pinned, cfg, dt_eff, 2);
     }
 }
@@ -176,7 +202,7 @@ void orc_physics_frames3(int64_t n, double* pos, double* vel, double* acc, doubl
                          const float* mass, const uint8_t* pinned, const orc_config* cfg, float dt_eff,
                          int64_t n_frames) {
     for (int64_t f = 0; f < n_frames; ++f) {
-        gravity_dim(n, pos, vel, mass, pinned, cfg->g, cfg->softening, acc, 3);
+        gravity_switch(n, pos, vel, mass, pinned, cfg, acc, 3);
         integrate_dim(n, pos, vel, acc, acc_prev, mass, pinned, cfg, dt_eff, 3);
     }
 }

@@ -81,6 +81,20 @@ void ref_set_config(void* h, double g, float softening, float max_speed, int int
     cfg->paused = false;
 }
 
+// The gravity solver switch (Config.hpp:17-18, Physics.hpp:212): Barnes-Hut above bh_threshold bodies.
+// ref_world_create() sets INT_MAX (direct sum); the reference's own default is 100 / 0.5.
+void ref_set_solver(void* h, int bh_threshold, float bh_theta) {
+    Config* cfg = static_cast<RefWorld*>(h)->w.get_mut<Config>();
+    cfg->bh_threshold = bh_threshold;
+    cfg->bh_theta = bh_theta;
+}
+
+void ref_get_solver_defaults(int* bh_threshold, float* bh_theta) {
+    Config cfg{};
+    *bh_threshold = cfg.bh_threshold;
+    *bh_theta = cfg.bh_theta;
+}
+
 void ref_get_defaults(double* g, float* softening, float* max_speed, int* integrator, float* fixed_dt,
                       float* time_scale, float* max_substep, int* max_substeps_per_frame) {
     Config cfg{};

@@ -74,6 +74,20 @@ struct nb_ctx {
     long long overlap_grid_calls = 0;   // calls that took the O(N) grid broad phase
     size_t staging_bytes = 0;
 
+    // ---- the reference's solver switch (Physics.hpp:212): Barnes-Hut above bh_threshold bodies ----
+    int solver = NB_SOLVER_DIRECT;
+    int bh_threshold = 100;             // Constants.hpp:90
+    float bh_theta = 0.5f;              // Constants.hpp:91
+    void* bh_scratch = nullptr;         // tree arrays, sort buffers
+    size_t bh_bytes = 0;
+    long long bh_capacity = 0;          // cells allocated
+    long long bh_rows = 0;              // body rows the scratch was laid out for
+    unsigned int* h_bh_ctl = nullptr;   // pinned mirror of the build's control words + walk statistics
+    bool bh_stats = false;
+    int bh_coop_ctas_per_sm = 0;
+    long long bh_passes = 0, bh_nodes = 0, bh_depth = 0, bh_live = 0;
+    unsigned long long bh_walk[3] = {0, 0, 0};  // cells popped, terms, exact accept tests (when bh_stats)
+
     int gen = 0;               // generation of pk[gen & 1]
     int mass_exp = 0;          // masses are packed as m * 2^-mass_exp
     bool uniform_mass = false; // every body that can attract has the same mass -> no m*w multiply in the kernel

@@ -55,13 +55,15 @@ class Diagnostics:
 
 
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
-           "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
+           "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
+SOLVER_DIRECT, SOLVER_REFERENCE = 0, 1
+REF_BH_THRESHOLD, REF_BH_THETA = 100, 0.5  # Constants.hpp:90-91
 
 _lib = None
 
@@ -97,6 +99,10 @@ def load_library(path=LIB_PATH):
     L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_default_config.argtypes = [C.POINTER(Config)]
     L.nb_set_precision.argtypes = [C.c_void_p, C.c_int]
+    L.nb_set_solver.argtypes = [C.c_void_p, C.c_int, C.c_int32, C.c_float]
+    L.nb_get_solver.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int32), C.POINTER(C.c_float)]
+    L.nb_solver_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    L.nb_solver_profile.argtypes = [C.c_void_p, C.c_int]
     L.nb_local_range.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_partition.argtypes = [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_compute_gravity.argtypes = [C.c_void_p]
@@ -212,6 +218,26 @@ class Physics:
     def set_precision(self, mode):
         """PRECISION_AUTO / PRECISION_FP32 / PRECISION_FP64_EXACT (include/nbody_b200.h)."""
         _check(self._L.nb_set_precision(self._h, int(mode)))
+
+    def set_solver(self, solver=SOLVER_REFERENCE, bh_threshold=REF_BH_THRESHOLD, bh_theta=REF_BH_THETA):
+        """Config::bh_threshold / bh_theta (Config.hpp:17-18). SOLVER_REFERENCE follows the reference's
+        switch (Physics.hpp:212): its float Barnes-Hut quadtree above bh_threshold bodies, bit-identical;
+        SOLVER_DIRECT (the default) always evaluates the all-pairs sum."""
+        _check(self._L.nb_set_solver(self._h, int(solver), int(bh_threshold), float(bh_theta)))
+
+    def get_solver(self):
+        s, t, th = C.c_int(), C.c_int32(), C.c_float()
+        _check(self._L.nb_get_solver(self._h, C.byref(s), C.byref(t), C.byref(th)))
+        return s.value, t.value, th.value
+
+    def solver_profile(self, enable=True):
+        _check(self._L.nb_solver_profile(self._h, 1 if enable else 0))
+
+    def solver_info(self):
+        """Tree of the last Barnes-Hut pass (and, after solver_profile(True), what its walks did)."""
+        v = (C.c_int64 * 8)()
+        _check(self._L.nb_solver_info(self._h, v))
+        return dict(passes=v[0], cells=v[1], depth=v[2], bodies=v[3], visited=v[4], terms=v[5], exact_tests=v[6])
 
     # ---- bodies ------------------------------------------------------------------------
     def upload(self, pos, vel, mass, pinned=None):
