@@ -89,6 +89,13 @@ class Oracle:
         fn(C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned), C.c_double(g), C.c_float(softening), _d(acc))
         return acc
 
+    def compute_gravity_cfg(self, pos, vel, mass, pinned, cfg, acc=None):
+        """compute_gravity with the solver switch of Physics.hpp:212 (cfg.bh_threshold / cfg.bh_theta), 2-D."""
+        n = pos.shape[0]
+        out = np.zeros((n, 2), np.float64) if acc is None else acc
+        self.lib.orc_compute_gravity_cfg(C.c_int64(n), _d(pos), _d(vel), _f(mass), _b(pinned), C.byref(cfg), _d(out))
+        return out
+
     def bh_gravity(self, pos, vel, mass, pinned=None, g=DEFAULTS["g"], softening=DEFAULTS["softening"],
                    theta=REF_BH_THETA, acc=None, with_stats=False):
         """Barnes-Hut branch of compute_gravity (Physics.hpp:212-230), 2-D. Raises if two gathered bodies

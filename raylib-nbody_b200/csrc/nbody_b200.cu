@@ -762,6 +762,14 @@ static bool tree_active(const nb_ctx* c) {
     return c->solver == NB_SOLVER_REFERENCE && c->world == 1 && c->dim == 2 && c->n > (long long)c->bh_threshold;
 }
 
+// The tree is the reference's 2-D code: a 3-D upload on its side of the switch has no defined result.
+static int check_solver(const nb_ctx* c) {
+    if (c->solver == NB_SOLVER_REFERENCE && c->dim != 2 && c->n > (long long)c->bh_threshold)
+        return fail(NB_ERR_INVALID, "NB_SOLVER_REFERENCE: the reference's Barnes-Hut branch is 2-D; upload with nb_upload "
+                                    "or select NB_SOLVER_DIRECT");
+    return NB_OK;
+}
+
 // Force evaluation and integrator moves in the reference's own FP64 sequence (the tree branch always is).
 bool use_exact(const nb_ctx* c) { return tree_active(c) || use_exact_precision(c); }
 
@@ -997,6 +1005,7 @@ extern "C" int nb_compute_gravity(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_compute_gravity: null context");
     if (c->n == 0) return NB_OK;  // Physics.hpp:208
     NB_CUDA(cudaSetDevice(c->device));
+    NB_TRY(check_solver(c));
     if (use_exact(c)) NB_TRY(exact_force(c));
     else NB_TRY(force_pass(c, kForceOnly, false, 0.0));
     c->acc_valid = true;
@@ -1025,6 +1034,7 @@ extern "C" int nb_integrate(nb_ctx* c, float dt) {
     if (!c) return fail(NB_ERR_INVALID, "nb_integrate: null context");
     if (c->n == 0) return NB_OK;
     NB_CUDA(cudaSetDevice(c->device));
+    NB_TRY(check_solver(c));
     float dt_sub;
     const int n_steps = nb_substep_plan(dt, c->cfg.max_substep, c->cfg.max_substeps_per_frame, &dt_sub);
     const double h = (double)dt_sub;
@@ -1065,6 +1075,7 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
     if (n_frames < 0) return fail(NB_ERR_INVALID, "nb_step: negative frame count");
     if (c->n == 0 || n_frames == 0) return NB_OK;
     NB_CUDA(cudaSetDevice(c->device));
+    NB_TRY(check_solver(c));
     float dt_sub;
     const int n_steps = nb_substep_plan(dt_eff, c->cfg.max_substep, c->cfg.max_substeps_per_frame, &dt_sub);
     const double h = (double)dt_sub;
