@@ -64,6 +64,13 @@ public:
         bool resident = false;    // mirror matches device state
         nb_config applied{};
         bool config_applied = false;
+        // NB_SOLVER_DIRECT: always the all-pairs sum (Config::bh_threshold ignored). NB_SOLVER_REFERENCE:
+        // honour Config::bh_threshold / bh_theta exactly like Physics.hpp:212 — above the threshold the
+        // reference's float Barnes-Hut quadtree, bit-identical, so frames equal the reference's at its
+        // DEFAULT settings (bh_threshold = 100).
+        int solver = NB_SOLVER_DIRECT;
+        int applied_solver = -1, applied_bh_threshold = 0;
+        float applied_bh_theta = 0.0f;
         long long uploads = 0, frames = 0;
         long long collision_checks = 0, collision_frames = 0;  // device detections / frames that ran the CPU merge
         // Verlet: the kick pass of frame k also accumulates the potential at the positions frame k+1 starts
@@ -115,6 +122,13 @@ public:
         c.integrator = cfg.integrator == 0 ? NB_INTEGRATOR_EULER : NB_INTEGRATOR_VERLET;  // Physics.hpp:273,294
         c.max_substep = cfg.max_substep;
         c.max_substeps_per_frame = cfg.max_substeps_per_frame;
+        if (d.applied_solver != d.solver || d.applied_bh_threshold != cfg.bh_threshold ||
+            std::memcmp(&d.applied_bh_theta, &cfg.bh_theta, sizeof(float)) != 0) {
+            check(nb_set_solver(d.ctx, d.solver, cfg.bh_threshold, cfg.bh_theta), "nb_set_solver");
+            d.applied_solver = d.solver;
+            d.applied_bh_threshold = cfg.bh_threshold;
+            d.applied_bh_theta = cfg.bh_theta;
+        }
         if (d.config_applied && std::memcmp(&c, &d.applied, sizeof(c)) == 0) return;
         check(nb_set_config(d.ctx, &c), "nb_set_config");
         d.diag_cached = false;
@@ -176,7 +190,8 @@ public:
         return true;
     }
 
-    // Physics::compute_gravity, Physics.hpp:183-261 (always the direct sum; bh_threshold is ignored).
+    // Physics::compute_gravity, Physics.hpp:183-261 (the direct sum, or the reference's switch when
+    // Device::solver == NB_SOLVER_REFERENCE).
     static void compute_gravity(const flecs::world& w, Device& d) {
         apply_config(d, *w.get<Config>());
         Bodies b = sync(w, d);
@@ -244,8 +259,9 @@ public:
     // sysB = reference systems 2+3 fused: one nb_step evaluates gravity and integrates, which is
     // what the gravity system followed by integrate() computes. Trails (system 4) stay with the
     // reference's renderer.
-    static void register_systems(const flecs::world& w, int device = 0) {
+    static void register_systems(const flecs::world& w, int device = 0, int solver = NB_SOLVER_DIRECT) {
         Device d;
+        d.solver = solver;
         check(nb_create(device, &d.ctx), "nb_create");
         w.set<Device>(d);
 

@@ -251,6 +251,76 @@ int main() {
         expect(tb < tr, "the binding's frame is faster than the reference's");
         PhysicsB200::shutdown(wb);
     }
+    // ---- E: the reference at its DEFAULT solver settings (bh_threshold = 100, bh_theta = 0.5): above 100
+    //         bodies compute_gravity is the float Barnes-Hut quadtree (Physics.hpp:212-230). The binding with
+    //         NB_SOLVER_REFERENCE reproduces those frames bit for bit.
+    for (int integrator : {1, 0}) {
+        std::printf("E. 4096-body disk, reference default solver (Barnes-Hut above %d bodies, theta %.2f), %s\n",
+                    nbody::constants::default_bh_threshold, (double)nbody::constants::default_bh_theta,
+                    integrator ? "Velocity Verlet" : "Semi-Implicit Euler");
+        flecs::world wr, wb;
+        make_config(wr, integrator);
+        make_config(wb, integrator);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0, NB_SOLVER_REFERENCE);
+        add_disk(wr, 4096, 21, 2.0e6f);
+        add_disk(wb, 4096, 21, 2.0e6f);
+        for (flecs::world* w : {&wr, &wb}) {
+            Config* cfg = w->get_mut<Config>();
+            cfg->bh_threshold = nbody::constants::default_bh_threshold;
+            cfg->bh_theta = nbody::constants::default_bh_theta;
+            cfg->time_scale = 3.0e4f;
+            cfg->max_substep = 100.0f;  // 3 substeps per frame
+        }
+        const float dt = wr.get<Config>()->fixed_dt;
+        for (int f = 0; f < 12; ++f) { wr.progress(dt); wb.progress(dt); }
+        Snapshot r = snap(wr), b = snap(wb);
+        expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel), "positions and velocities bit-identical after 12 frames");
+        expect(bitwise(r.acc, b.acc) && (integrator == 0 || bitwise(r.acc_prev, b.acc_prev)),
+               "accelerations (float-valued tree sums) bit-identical");
+        // an external edit and a change of the opening angle mid-run
+        for (flecs::world* w : {&wr, &wb}) {
+            int k = 0;
+            w->each([&](Velocity& v) { if (k++ == 9) v.value.x += 50.0; });
+            w->get_mut<Config>()->bh_theta = 0.8f;
+        }
+        for (int f = 0; f < 8; ++f) { wr.progress(dt); wb.progress(dt); }
+        r = snap(wr); b = snap(wb);
+        expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel) && bitwise(r.acc, b.acc),
+               "still bit-identical after an edit and bh_theta = 0.8");
+        const auto* dr = wr.get<Physics::Diagnostics>();
+        const auto* db = wb.get<Physics::Diagnostics>();
+        expect(dr && db && dr->ok && db->ok && std::fabs(db->energy - dr->energy) <= 1e-6 * std::fabs(dr->energy),
+               "frame diagnostics agree to 1e-6 (direct-sum potential in both)");
+        expect(wb.get<PhysicsB200::Device>()->uploads == 2, "two uploads: the first frame and the edit");
+        PhysicsB200::shutdown(wb);
+    }
+    {
+        flecs::world wr, wb;
+        make_config(wr, 1);
+        make_config(wb, 1);
+        Physics::register_systems(wr);
+        PhysicsB200::register_systems(wb, 0, NB_SOLVER_REFERENCE);
+        add_disk(wr, 16384, 5, 2.0e6f, false);
+        add_disk(wb, 16384, 5, 2.0e6f, false);
+        for (flecs::world* w : {&wr, &wb}) {
+            w->get_mut<Config>()->bh_threshold = nbody::constants::default_bh_threshold;
+            w->get_mut<Config>()->time_scale = 3.0e4f;
+        }
+        const float dt = wr.get<Config>()->fixed_dt;
+        auto seconds = [&](flecs::world& w, int frames) {
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int f = 0; f < frames; ++f) w.progress(dt);
+            return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / frames;
+        };
+        wb.progress(dt);
+        wr.progress(dt);
+        const double tr = seconds(wr, 2), tb = seconds(wb, 20);
+        std::printf("16384-body frame at the reference's default settings (Barnes-Hut gravity, O(N^2) collision test and "
+                    "diagnostics): reference %.3f s, binding %.6f s  (x%.0f)\n", tr, tb, tr / tb);
+        expect(tb < tr, "the binding's default-settings frame is faster than the reference's");
+        PhysicsB200::shutdown(wb);
+    }
     std::printf(failures ? "DROPIN CHECK FAILED (%d)\n" : "DROPIN CHECK PASSED\n", failures);
     return failures ? 1 : 0;
 }

@@ -40,6 +40,7 @@ constexpr int kBhMaxLevels = 320;  // a float half-size underflows to 0 after < 
 constexpr int kBhBuildThreads = 256;
 constexpr int kBhWalkThreads = 128;
 constexpr int kBhKeyLevels = 16;   // tree levels in the Z-order key
+constexpr int kBhHistCells = 4096; // levels with at most this many new cells count bodies per CTA first
 
 // control words (device, mirrored to pinned host memory after the build)
 enum BhCtl { kBhNodes = 0, kBhError, kBhLive, kBhDepth, kBhMinX, kBhMaxX, kBhMinY, kBhMaxY, kBhCtlWords };
@@ -57,7 +58,17 @@ struct BhTree {
     int* level_begin;    // [kBhMaxLevels + 2]
     unsigned int* ctl;   // BhCtl
     int capacity;        // cells allocated
+    unsigned long long* trace;  // developer knob NB_BH_TRACE: globaltimer stamps of the build's phases, else null
 };
+
+__device__ __forceinline__ void bh_stamp(const BhTree& t, long long gid, int& slot) {
+    if (gid == 0 && t.trace) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        t.trace[slot] = now;
+    }
+    ++slot;
+}
 
 __device__ __forceinline__ unsigned int float_order_key(float f) {
     const unsigned int u = __float_as_uint(f);
@@ -73,9 +84,12 @@ __device__ __forceinline__ int bh_quadrant(float2 c, float2 p) { return (p.x > c
 // Build + aggregate in one cooperative launch (grid = resident CTAs only).
 __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, BhTree t) {
     cg::grid_group grid = cg::this_grid();
+    __shared__ int s_hist[kBhHistCells];
     const long long gsz = (long long)gridDim.x * blockDim.x;
     const long long gid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const int n = (int)s.n;
+    int stamp = 1;
+    bh_stamp(t, gid, stamp);
 
     // ---- gather filter (Physics.hpp:197-205), float casts (:217), bounding box (SpatialPartition.hpp:40-49)
     if (gid == 0) {
@@ -102,7 +116,6 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
             t.bpos[i] = p;
             t.cur[i] = 0;
             t.key[i] = 0u;
-            t.link[0].x = -2 - (int)i;  // only meaningful when this is the only body
             const unsigned int kx = float_order_key(p.x), ky = float_order_key(p.y);
             lo_x = min(lo_x, kx); hi_x = max(hi_x, kx);
             lo_y = min(lo_y, ky); hi_y = max(hi_y, ky);
@@ -138,6 +151,7 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
         t.level_begin[1] = 1;
     }
     grid.sync();
+    bh_stamp(t, gid, stamp);
 
     // ---- grow the tree one level per iteration (the fixed point of the insertions, :109-167)
     int lb = 0, le = 1, level = 0;
@@ -165,6 +179,7 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
             t.link[k].x = base;
         }
         grid.sync();
+        bh_stamp(t, gid, stamp);
         const int new_le = (int)min(t.ctl[kBhNodes], (unsigned int)t.capacity);
         const bool stop = new_le == le || t.ctl[kBhError] != kBhOk || level + 1 >= kBhMaxLevels;
         if (stop) {
@@ -174,12 +189,22 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
             }
             break;
         }
-        // every body still travelling steps into the child that contains it (:127,:148,:153)
+        // every body still travelling steps into the child that contains it (:127,:148,:153). Near the root a
+        // level has few cells and every body is still travelling: counting straight into global memory would
+        // serialise a million atomics on a handful of addresses (measured: 0.4-0.6 ms per level for the first
+        // four levels at N = 2^20), so those levels count in a per-CTA shared histogram first.
+        const int n_new = new_le - le;
+        const bool hist = n_new <= kBhHistCells;
+        if (hist) {
+            for (int k = threadIdx.x; k < n_new; k += blockDim.x) s_hist[k] = 0;
+            __syncthreads();
+        }
         for (long long i = gid; i < n; i += gsz) {
             const int c = t.cur[i];
             if (c < 0) continue;
             const int first = t.link[c].x;
-            if (first < 0) {  // alone in its cell: placed
+            if (first < 0) {  // alone in its cell: placed, and the cell learns whose it is
+                t.link[c].x = -2 - (int)i;
                 t.cur[i] = -1;
                 if (level > 0 && level < kBhKeyLevels) t.key[i] <<= 2 * (kBhKeyLevels - level);
                 continue;
@@ -187,22 +212,32 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
             const int q = bh_quadrant(t.centre[c], t.bpos[i]);
             const int child = first + q;
             t.cur[i] = child;
-            t.link[child].x = -2 - (int)i;  // survives only if the body stays alone here
-            atomicAdd(&t.count[child], 1);
+            if (hist) atomicAdd(&s_hist[child - le], 1);
+            else atomicAdd(&t.count[child], 1);
             if (level < kBhKeyLevels) t.key[i] = (t.key[i] << 2) | (unsigned int)q;
+        }
+        if (hist) {
+            __syncthreads();
+            for (int k = threadIdx.x; k < n_new; k += blockDim.x)
+                if (s_hist[k]) atomicAdd(&t.count[le + k], s_hist[k]);
         }
         lb = le;
         le = new_le;
         ++level;
         if (gid == 0) t.level_begin[level + 1] = le;
         grid.sync();
+        bh_stamp(t, gid, stamp);
     }
     grid.sync();  // error word, level_begin and depth visible to everyone
     if (t.ctl[kBhError] != kBhOk) return;  // uniform
-    // bodies placed on the deepest level: left-align their keys like the others
-    if (level > 0 && level < kBhKeyLevels)
-        for (long long i = gid; i < n; i += gsz)
-            if (t.cur[i] >= 0) t.key[i] <<= 2 * (kBhKeyLevels - level);
+    // bodies still travelling sit alone in cells of the deepest level: place them (keys left-aligned like the others)
+    for (long long i = gid; i < n; i += gsz) {
+        const int c = t.cur[i];
+        if (c < 0) continue;
+        t.link[c].x = -2 - (int)i;
+        if (level > 0 && level < kBhKeyLevels) t.key[i] <<= 2 * (kBhKeyLevels - level);
+    }
+    grid.sync();
 
     // ---- mass and centre of mass, deepest level first (:178-220)
     for (int lv = level; lv >= 0; --lv) {
@@ -240,6 +275,8 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
         }
         if (lv > 0) grid.sync();
     }
+    bh_stamp(t, gid, stamp);
+    if (gid == 0 && t.trace) t.trace[0] = (unsigned long long)stamp;
 }
 
 // One walk per body (Physics.hpp:224-230 + SpatialPartition.hpp:63-106). order[]: body rows in Z-order.
@@ -264,33 +301,32 @@ __global__ void __launch_bounds__(kBhWalkThreads) bh_walk_kernel(StateView s, Bh
                 const float4* __restrict__ cell = t.cell;
                 const int2* __restrict__ link = t.link;
                 int node = 0;
+                // One cell per trip. The trip is written as straight-line code with two rarely/partly taken
+                // blocks (the FP64 re-evaluation of a borderline accept test, the accepted term) so that a warp
+                // pays for two reconvergence points per cell instead of one per source-level branch.
                 while (node >= 0) {
                     const float4 c = __ldg(&cell[node]);
                     const int2 l = __ldg(&link[node]);
                     if (STATS) ++n_pop;
-                    int next = l.y;
-                    bool term = false;
-                    if (c.z > 0.f) {  // :72 (an empty leaf has mass 0)
-                        if (l.x < 0) {
-                            term = (-2 - l.x) != i;  // :75
-                        } else {
-                            // accept test :88-91, in FP32 when that is decisive
-                            const float fdx = c.x - p.x, fdy = c.y - p.y;
-                            const float d2 = fmaf(fdx, fdx, fdy * fdy);
-                            const float q = (c.w + c.w) * rsqrtf(d2);
-                            bool accept;
-                            if (fast && d2 > 1e-30f && d2 < 1e30f && (q < th_lo || q > th_hi)) {
-                                accept = q < th_lo;
-                            } else {
-                                const double dx = __dsub_rn((double)c.x, tx), dy = __dsub_rn((double)c.y, ty);
-                                const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-                                accept = __ddiv_rn(__dmul_rn((double)c.w, 2.0), dist) < theta;
-                                if (STATS) ++n_exact;
-                            }
-                            term = accept;
-                            if (!accept) next = l.x + 3;  // open: children 3,2,1,0
-                        }
+                    const bool massive = c.z > 0.f;   // :72 (an empty leaf has mass 0)
+                    const bool inner = l.x >= 0;
+                    // accept test :88-91 in FP32 (harmless on a leaf: its result is not used there)
+                    const float fdx = c.x - p.x, fdy = c.y - p.y;
+                    const float d2 = fmaf(fdx, fdx, fdy * fdy);
+                    float rs;
+                    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(d2));
+                    const float q = (c.w + c.w) * rs;
+                    const bool decisive = fast && d2 > 1e-30f && d2 < 1e30f && (q < th_lo || q > th_hi);
+                    bool accept = q < th_lo;
+                    if (massive && inner && !decisive) {  // a handful of cells per million
+                        const double dx = __dsub_rn((double)c.x, tx), dy = __dsub_rn((double)c.y, ty);
+                        const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+                        accept = __ddiv_rn(__dmul_rn((double)c.w, 2.0), dist) < theta;
+                        if (STATS) ++n_exact;
                     }
+                    // a leaf contributes unless it is empty or the target itself (:75); a cell when accepted
+                    const bool term = massive && (inner ? accept : (-2 - l.x) != i);
+                    node = (massive && inner && !accept) ? l.x + 3 : l.y;  // open: children 3,2,1,0
                     if (term) {
                         const double dx = __dsub_rn((double)c.x, tx), dy = __dsub_rn((double)c.y, ty);
                         const double r2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), eps2);
@@ -301,7 +337,6 @@ __global__ void __launch_bounds__(kBhWalkThreads) bh_walk_kernel(StateView s, Bh
                         afy = __fadd_rn(afy, __double2float_rn(__dmul_rn(__dmul_rn(gm, dy), inv_r3)));
                         if (STATS) ++n_term;
                     }
-                    node = next;
                 }
             }
             s.a[0][i] = (double)afx;  // :228-229, :260; a pinned body gets 0

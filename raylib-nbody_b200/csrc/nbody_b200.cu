@@ -817,7 +817,7 @@ namespace {
 inline size_t bh_align(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct BhLayout {
-    size_t bpos, centre, cell, link, count, cur, key, key_out, order_in, order_out, level, ctl, visits, cub, total;
+    size_t bpos, centre, cell, link, count, cur, key, key_out, order_in, order_out, level, ctl, visits, trace, cub, total;
     size_t cub_bytes;
 };
 
@@ -828,6 +828,7 @@ BhLayout bh_layout(long long rows, long long cells) {
     L.ctl = take(sizeof(unsigned int) * kBhCtlWords);
     L.visits = take(sizeof(unsigned long long) * 4);
     L.level = take(sizeof(int) * (kBhMaxLevels + 2));
+    L.trace = take(sizeof(unsigned long long) * (2 * kBhMaxLevels + 16));
     L.bpos = take(sizeof(float2) * (size_t)rows);
     L.cur = take(sizeof(int) * (size_t)rows);
     L.key = take(sizeof(unsigned int) * (size_t)rows);
@@ -879,6 +880,8 @@ BhTree bh_view(const nb_ctx* c, const BhLayout& L) {
     t.level_begin = reinterpret_cast<int*>(b + L.level);
     t.ctl = reinterpret_cast<unsigned int*>(b + L.ctl);
     t.capacity = (int)c->bh_capacity;
+    static const bool trace = getenv("NB_BH_TRACE") != nullptr;  // developer knob: per-phase times on stderr
+    t.trace = trace ? reinterpret_cast<unsigned long long*>(b + L.trace) : nullptr;
     return t;
 }
 
@@ -913,6 +916,13 @@ static int tree_force(nb_ctx* c) {
         NB_CUDA(cudaMemcpyAsync(c->h_bh_ctl, t.ctl, sizeof(unsigned int) * kBhCtlWords, cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
         const unsigned int err = c->h_bh_ctl[kBhError];
+        if (t.trace) {
+            std::vector<unsigned long long> tr(2 * kBhMaxLevels + 16);
+            NB_CUDA(cudaMemcpy(tr.data(), t.trace, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[bh trace] %d stamps, us since start:", (int)tr[0] - 1);
+            for (unsigned long long k = 2; k < tr[0] && k < tr.size(); ++k) fprintf(stderr, " %.1f", (double)(tr[k] - tr[1]) * 1e-3);
+            fprintf(stderr, "\n");
+        }
         if (err == kBhOverflow) {  // more cells than allocated: the count the build reached is a lower bound
             cells = std::max<long long>(2 * c->bh_capacity, (long long)c->h_bh_ctl[kBhNodes] + 4096);
             continue;
