@@ -247,6 +247,50 @@ def run_ours(args):
         planar = {"value": float(n) * n * 2 / (p_ms * 1e-3), "unit": UNIT, "steps": 2,
                   "note": "2-D reference layout (z = 0): 8 FMA-pipe ops per pair; counted as interactions, not as 20-FLOP work"}
 
+    tree = None
+    if world == 1 and args.tree:
+        # The reference's DEFAULT solver at this body count: above bh_threshold = 100 bodies its
+        # compute_gravity is a float Barnes-Hut quadtree (Physics.hpp:212-230), reproduced bit for bit
+        # by NB_SOLVER_REFERENCE. Not the headline metric (a tree pass does ~600 cell visits per
+        # body, not N interactions): reported as time per Verlet step beside the reference's own.
+        p2, v2, m2 = pkg.scenarios.plummer(n, seed=1234, dim=2)
+        pt = pkg.Physics(local_rank)
+        pt.set_config(softening=eps, integrator=1)
+        pt.set_solver(pkg.SOLVER_REFERENCE, pkg.REF_BH_THRESHOLD, pkg.REF_BH_THETA)
+        pt.solver_profile(True)
+        pt.upload(p2, v2, m2)
+        pt.step(dt, 1)
+        info = pt.solver_info()
+        pt.solver_profile(False)
+        pt.step(dt, 2)
+        pt.synchronize()
+        pt.timer_begin()
+        pt.step(dt, 10)
+        t_ms = pt.timer_end() / 10
+        pt.close()
+        tree = {"ms_per_step": t_ms, "steps_per_s": 1e3 / t_ms, "bodies_per_s": n * 1e3 / t_ms,
+                "cells": info["cells"], "depth": info["depth"], "cells_visited_per_body": info["visited"] / n,
+                "terms_per_body": info["terms"] / n, "cell_visits_per_s": info["visited"] * 1e3 / t_ms,
+                "note": "NB_SOLVER_REFERENCE: the reference's default Barnes-Hut branch (bh_threshold 100, theta 0.5), "
+                        "bit-identical accelerations; 2-D projection of the same sphere; one tree build + walk per step"}
+        if rank == 0 and args.cpu_sample > 0:
+            from oracle import bindings as ob
+            if ob.have_reference():
+                r = ob.Reference()
+                r.set_config(softening=eps)
+                r.set_solver(ob.REF_BH_THRESHOLD, ob.REF_BH_THETA)
+                r.load_bodies(p2, v2, m2)
+                t0 = time.perf_counter()
+                r.compute_gravity()
+                tree["cpu_seconds_per_pass"] = time.perf_counter() - t0
+                tree["cpu_kind"] = "reference"
+                r.close()
+            else:
+                t0 = time.perf_counter()
+                ob.Oracle().bh_gravity(p2, v2, m2, softening=eps)
+                tree["cpu_seconds_per_pass"] = time.perf_counter() - t0
+                tree["cpu_kind"] = "port"
+
     if rank == 0:
         props_sms = ph.device_info()["sm_count"]
         peaks = {}
@@ -286,6 +330,7 @@ def run_ours(args):
             "pct_fp32_peak": 100.0 * value * FLOPS_PER_INTERACTION / (peak * 1e12 * world),
             "steps_per_s": 1e3 * args.steps / total_ms,
             "kernel_variant": "uniform-mass (all bodies of config 4 have equal mass)", "general_mass": general, "planar_2d": planar,
+            "reference_solver": tree,
             "roofline": roof, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
@@ -345,8 +390,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=1 << 20, help="bodies (BASELINE metric: 2^20)")
-    ap.add_argument("--cpu-sample", type=int, default=32768, help="bodies in the cpu_baseline sample (0 = skip)")
-    ap.add_argument("--ref-sample", type=int, default=16384, help="bodies per step of --impl reference")
+    ap.add_argument("--no-tree", dest="tree", action="store_false",
+                    help="skip the extra figure for the reference's default Barnes-Hut solver")
+    # sample sizes are deliberately not powers of two: the reference's loop streams pos[j] and acc[j]
+    # (both 16 B/body); at N = 16384 the two arrays sit 256 KiB apart and alias in the host caches,
+    # which made that size 2-4x slower per interaction than its neighbours (profiles/r01_cpu_baseline_table.txt)
+    ap.add_argument("--cpu-sample", type=int, default=30000, help="bodies in the cpu_baseline sample (0 = skip)")
+    ap.add_argument("--ref-sample", type=int, default=20000, help="bodies per step of --impl reference")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
