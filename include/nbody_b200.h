@@ -203,6 +203,30 @@ int nb_zero_net_momentum(nb_ctx* ctx);
  * Single-GPU contexts. Synchronises. */
 int nb_count_overlaps(nb_ctx* ctx, const double* radius, int64_t* n_overlaps, int64_t* first_pair);
 
+/* Collision::resolve in its default merge mode (src/systems/Collision.hpp:49-132) on the bodies the
+ * context holds (2-D uploads), with the reference's outcome bit for bit: which bodies are destructed,
+ * and the survivors' new Mass (float), Velocity, Position (momentum- and mass-weighted, :107-112),
+ * Pinned (:120) and radius (:37-46). Every pair test runs on the device; the merges, which the
+ * reference applies one after another with the survivor's CHANGED position, mass and radius feeding
+ * the following tests (and with a row that keeps running after its own body died, :76), are replayed
+ * on the host in the reference's order from the device's detections.
+ *   radius[i]   in: Collision::radius_of per body on entry (:28-35)
+ *   density[i]  in: the Density component, or 5510 (Constants.hpp:34)
+ *   alive[i]    out: 0 where the reference would destruct the body (:124)
+ *   changed[i]  out: 1 where a body survived a merge; its pos_xy/vel_xy/mass/pinned/radius_out entries
+ *               are then written (others are left untouched) and the caller zeroes its Acceleration
+ *               and PrevAcceleration (:118-119)
+ *   merge_log   out (may be NULL): the merges in the order the reference performs them, as pairs
+ *               {survivor, absorbed}; at most merge_log_cap pairs are written, n_merges is the full
+ *               count. An ECS caller needs the order: flecs applies the deferred destruct() calls in
+ *               the order they were issued, and the order decides the row order of the bodies left
+ * The device state is not modified: the caller applies the result to its bodies and uploads the new
+ * world. When no pair overlaps (the common frame) the call costs one detection pass and returns
+ * n_merges = 0. Single-GPU contexts. Synchronises. */
+int nb_resolve_collisions(nb_ctx* ctx, const double* radius, const double* density, int64_t* n_merges,
+                          uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
+                          uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap);
+
 /* Substep plan of Physics.hpp:268-271 (float arithmetic). Host-only helper. */
 int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub);
 

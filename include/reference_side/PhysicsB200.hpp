@@ -7,8 +7,8 @@
 //   Physics::register_systems     src/systems/Physics.hpp:32-64
 //   Physics::compute_gravity      :183-261        Physics::integrate          :263-327
 //   Physics::compute_diagnostics  :117-177        Physics::zero_net_momentum  :66-85
-// by gather -> C-ABI call -> scatter. No reference code is copied: the reference keeps
-// Collision::resolve (out of scope), trails, UI and rendering.
+// and Collision::resolve (src/systems/Collision.hpp:49-132) by gather -> C-ABI call -> scatter. No reference
+// code is copied: the reference keeps trails, UI and rendering.
 //
 // Device residency: the shim keeps a host mirror of what it last scattered.
 // When a frame's gather equals the mirror nothing was edited from outside (UI, drag, merge,
@@ -72,7 +72,7 @@ public:
         int applied_solver = -1, applied_bh_threshold = 0;
         float applied_bh_theta = 0.0f;
         long long uploads = 0, frames = 0;
-        long long collision_checks = 0, collision_frames = 0;  // device detections / frames that ran the CPU merge
+        long long collision_checks = 0, collision_frames = 0, merges = 0;  // device passes / frames with a merge / merges
         // Verlet: the kick pass of frame k also accumulates the potential at the positions frame k+1 starts
         // from, so its fused diagnostics ARE frame k+1's frame-start diagnostics unless something was edited
         bool diag_cached = false;
@@ -232,30 +232,66 @@ public:
         d.mirror.vel = b.vel;
     }
 
-    // Collision::resolve (Collision.hpp:49-203) with its O(N^2) detection phase on the device: the
-    // reference's own merge code runs only on frames where some pair overlaps (nb_count_overlaps
-    // evaluates Collision.hpp:76-84 exactly), so merge semantics are the reference's, bit for bit.
+    // Collision::resolve (Collision.hpp:49-132, merge mode) through nb_resolve_collisions: every pair test runs
+    // on the device, the merges are replayed in the reference's order (bit-identical outcome, including the
+    // rows that keep running after their body died), and the outcome is applied to the components with the
+    // same calls the reference makes: immediate writes through get_mut, deferred destruct (:115-124) — so the
+    // diagnostics that follow in the same system see what they see in the reference (survivors updated, the
+    // destructed bodies still present until the system ends).
     static void resolve_collisions(const flecs::world& w, Device& d) {
         apply_config(d, *w.get<Config>());
         Bodies b = sync(w, d);
-        if (b.size() < 2) return;  // Collision.hpp:70
-        std::vector<double> radius;
-        radius.reserve(b.size());
+        const size_t n = b.size();
+        if (n < 2) return;  // Collision.hpp:70
+        std::vector<flecs::entity> ents;
+        std::vector<double> radius, density;
+        ents.reserve(n); radius.reserve(n); density.reserve(n);
         w.each([&](const flecs::entity e, const Position&, const Velocity&, const Acceleration&,
                    const PrevAcceleration&, const Mass& m, const Pinned&) {
+            ents.push_back(e);
             radius.push_back(nbody::systems::Collision::radius_of(e, m));  // Collision.hpp:28-35
+            double rho = nbody::constants::body_density;                   // :31-32
+            if (const auto* dd = e.get<Density>()) rho = dd->value;
+            density.push_back(rho);
         });
-        int64_t overlaps = 0;
-        check(nb_count_overlaps(d.ctx, radius.data(), &overlaps, nullptr), "nb_count_overlaps");
+        std::vector<uint8_t> alive(n), changed(n), pinned(n);
+        std::vector<double> pos(2 * n), vel(2 * n), rad(n);
+        std::vector<float> mass(n);
+        int64_t merges = 0;
+        std::vector<int64_t> log(2 * 4 * n);
+        for (;;) {
+            check(nb_resolve_collisions(d.ctx, radius.data(), density.data(), &merges, alive.data(), changed.data(),
+                                        pos.data(), vel.data(), mass.data(), pinned.data(), rad.data(), log.data(),
+                                        (int64_t)(log.size() / 2)),
+                  "nb_resolve_collisions");
+            if ((size_t)merges * 2 <= log.size()) break;
+            log.resize(2 * (size_t)merges);  // more merges than bodies x 4 (rows of dead bodies): once more with room
+        }
         d.collision_checks++;
-        if (overlaps == 0) return;
+        if (merges == 0) return;
         d.collision_frames++;
-        nbody::systems::Collision::resolve(w);  // edits components; the next sync() sees them and re-uploads
+        d.merges += merges;
+        // Per merge, in the reference's order, the very calls it makes (:115-124). The component writes go through
+        // get_mut and take effect at once, so writing the survivor's FINAL values at each of its merges leaves the
+        // same components; but every get_mut / set / destruct inside a system also enters flecs' command queue,
+        // and the queue's order decides the order of the table moves and swap-removes at the end of the system —
+        // i.e. the row order of the bodies that are left. Same calls in the same order => same rows.
+        for (int64_t k = 0; k < merges; ++k) {
+            const size_t i = (size_t)log[2 * k];
+            flecs::entity sv = ents[i], dead = ents[(size_t)log[2 * k + 1]];
+            if (auto* mp = sv.get_mut<Mass>()) mp->value = mass[i];
+            if (auto* vp = sv.get_mut<Velocity>()) vp->value = DVec2{vel[2 * i], vel[2 * i + 1]};
+            if (auto* pp = sv.get_mut<Position>()) pp->value = DVec2{pos[2 * i], pos[2 * i + 1]};
+            if (auto* ap = sv.get_mut<Acceleration>()) ap->value = DVec2{0.0, 0.0};
+            if (auto* a0 = sv.get_mut<PrevAcceleration>()) a0->value = DVec2{0.0, 0.0};
+            if (auto* pinp = sv.get_mut<Pinned>()) pinp->value = pinned[i] != 0;
+            if (auto* rp = sv.get_mut<Radius>()) rp->value = rad[i]; else sv.set<Radius>({rad[i]});  // :42-46
+            dead.destruct();
+        }
     }
 
     // ---- the frame, Physics.hpp:32-64 -------------------------------------------------------
-    // sysA = reference system 1 (collision detection and diagnostics on the device; the merge itself
-    // stays reference CPU code and only runs when a pair overlaps),
+    // sysA = reference system 1 (collision pass and diagnostics on the device),
     // sysB = reference systems 2+3 fused: one nb_step evaluates gravity and integrates, which is
     // what the gravity system followed by integrate() computes. Trails (system 4) stay with the
     // reference's renderer.

@@ -45,6 +45,7 @@ DEFAULTS = dict(g=6.67430e-11, softening=4.0, max_speed=0.0, integrator=1, fixed
 # Solver switch (Config.hpp:17-18). The reference's own defaults are REF_BH_THRESHOLD / REF_BH_THETA
 # (Constants.hpp:90-91); the checkers default to "never" so the direct sum — the north-star path — is
 # what a test gets unless it asks for the tree.
+BODY_DENSITY = 5510.0  # Constants.hpp:34
 BH_NEVER = 2**31 - 1
 REF_BH_THRESHOLD = 100
 REF_BH_THETA = 0.5
@@ -149,6 +150,31 @@ class Oracle:
                                         _d(np.ascontiguousarray(radius, np.float64)), first)
         return int(n), ((first[0], first[1]) if n else None)
 
+    def radius_from_mass(self, mass, density=None):
+        """Collision::radius_of for a body without a Radius component (Collision.hpp:30-34)."""
+        n = len(mass)
+        rho = np.full(n, BODY_DENSITY) if density is None else np.ascontiguousarray(density, np.float64)
+        out = np.zeros(n)
+        self.lib.orc_radius_from_mass(C.c_int64(n), _f(np.ascontiguousarray(mass, np.float32)), _d(rho), _d(out))
+        return out
+
+    def resolve_collisions(self, pos, vel, mass, pinned, radius, density=None, with_log=False):
+        """Collision::resolve, merge mode (Collision.hpp:49-132). Returns (merges, alive, changed, pos, vel, mass,
+        pinned, radius) with the survivors' new values; inputs are not modified."""
+        n = pos.shape[0]
+        p, v = np.array(pos, np.float64, order="C"), np.array(vel, np.float64, order="C")
+        m, pin = np.array(mass, np.float32), np.array(pinned if pinned is not None else np.zeros(n), np.uint8)
+        r = np.array(radius, np.float64)
+        rho = np.full(n, BODY_DENSITY) if density is None else np.array(density, np.float64)
+        alive, changed = np.ones(n, np.uint8), np.zeros(n, np.uint8)
+        self.lib.orc_resolve_collisions.restype = C.c_int64
+        log = np.zeros((8 * max(n, 1), 2), np.int64)
+        k = self.lib.orc_resolve_collisions(C.c_int64(n), _d(p), _d(v), _f(m), _b(pin), _d(r), _d(rho), _b(alive), _b(changed),
+                                            log.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int64(log.shape[0]))
+        if with_log:
+            return int(k), alive, changed, p, v, m, pin, r, log[:int(k)]
+        return int(k), alive, changed, p, v, m, pin, r
+
     def zero_net_momentum(self, vel, mass, pinned=None):
         n = vel.shape[0]
         self.lib.orc_zero_net_momentum(C.c_int64(n), _d(vel), _f(mass), _b(pinned))
@@ -221,6 +247,22 @@ class Reference:
         """Collision::resolve with explicit Radius components; returns the number of bodies left."""
         self.lib.ref_collision_resolve.restype = C.c_int64
         return int(self.lib.ref_collision_resolve(self.h, _d(np.ascontiguousarray(radius, np.float64))))
+
+    def collision_resolve_full(self, radius, density=None):
+        """Collision::resolve with per-body results in load order. radius < 0: no Radius component (derived from
+        mass and density). Returns (alive, pos, vel, acc, mass, pinned, radius_after, visit_order); visit_order[k] is
+        the load index of the k-th body the pass visits (flecs iterates table by table)."""
+        n = self.num_bodies()
+        alive = np.zeros(n, np.uint8)
+        pos, vel, acc = np.zeros((n, 2)), np.zeros((n, 2)), np.zeros((n, 2))
+        mass, pinned, rout = np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros(n)
+        rin = np.ascontiguousarray(radius, np.float64)
+        rho = None if density is None else np.ascontiguousarray(density, np.float64)
+        self.lib.ref_collision_resolve_full.restype = C.c_int64
+        order = np.zeros(n, np.int64)
+        self.lib.ref_collision_resolve_full(self.h, _d(rin), _d(rho), _b(alive), _d(pos), _d(vel), _d(acc), _f(mass),
+                                            _b(pinned), _d(rout), order.ctypes.data_as(C.POINTER(C.c_int64)))
+        return alive, pos, vel, acc, mass, pinned, rout, order
 
     def num_bodies(self):
         return self.lib.ref_num_bodies(self.h)

@@ -200,30 +200,66 @@ int main() {
         expect(!wb.get<Physics::Diagnostics>()->ok, "Diagnostics.ok is false");
         PhysicsB200::shutdown(wb);
     }
-    // ---- C: real radii: collision detection on the device, merges by the reference's own code ---------
-    {
+    // ---- C: real radii: the whole collision pass (Collision.hpp:49-132) through nb_resolve_collisions ------
+    for (int dense = 0; dense < 2; ++dense) {
         flecs::world wr, wb;
         make_config(wr, 1);
         make_config(wb, 1);
         Physics::register_systems(wr);
         PhysicsB200::register_systems(wb, 0);
-        add_disk(wr, 400, 7, 2.0e6f, true);
-        add_disk(wb, 400, 7, 2.0e6f, true);
-        for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->time_scale = 3.0e4f;
+        const int n0 = dense ? 500 : 400, frames = dense ? 15 : 40;  // <= 512 bodies: the FP64-exact gravity path, so states can be compared bitwise
+        add_disk(wr, n0, 7, 2.0e6f, true);
+        add_disk(wb, n0, 7, 2.0e6f, true);
+        for (flecs::world* w : {&wr, &wb}) {
+            w->get_mut<Config>()->time_scale = 3.0e4f;
+            if (dense) {  // puffy bodies (Density component, Collision.hpp:31-32): chains of merges within one frame
+                std::vector<flecs::entity> es;
+                w->each([&](flecs::entity e, Position&) { es.push_back(e); });
+                for (auto& e : es) e.set<Density>({0.5});
+            }
+        }
         const float dt = wr.get<Config>()->fixed_dt;
-        for (int f = 0; f < 40; ++f) {
+        double worst_diag = 0.0;
+        bool diag_ok = true;
+        for (int f = 0; f < frames; ++f) {
             wr.progress(dt);
             wb.progress(dt);
+            // frame-start diagnostics, merge frames included (there the destructed bodies are still counted, in
+            // both worlds, because destruct() is deferred to the end of the system)
+            const auto* dr = wr.get<Physics::Diagnostics>();
+            const auto* db = wb.get<Physics::Diagnostics>();
+            if (getenv("NB_DROPIN_DEBUG")) {
+                const Snapshot sr = snap(wr), sb = snap(wb);
+                const auto* dv = wb.get<PhysicsB200::Device>();
+                std::printf("    frame %d: bodies %zu / %zu, merges so far %lld, pos %s vel %s acc %s, E %.17g / %.17g\n", f,
+                            sr.pos.size() / 2, sb.pos.size() / 2, dv->merges, bitwise(sr.pos, sb.pos) ? "same" : "DIFF",
+                            bitwise(sr.vel, sb.vel) ? "same" : "DIFF", bitwise(sr.acc, sb.acc) ? "same" : "DIFF",
+                            dr ? dr->energy : 0.0, db ? db->energy : 0.0);
+                if (sr.pos.size() == sb.pos.size() && !bitwise(sr.pos, sb.pos)) {
+                    int shown = 0;
+                    for (size_t k = 0; k < sr.pos.size() / 2 && shown < 4; ++k)
+                        if (sr.pos[2 * k] != sb.pos[2 * k] || sr.pos[2 * k + 1] != sb.pos[2 * k + 1]) {
+                            std::printf("      row %zu: ref (%.17g, %.17g) binding (%.17g, %.17g)\n", k, sr.pos[2 * k], sr.pos[2 * k + 1],
+                                        sb.pos[2 * k], sb.pos[2 * k + 1]);
+                            ++shown;
+                        }
+                }
+            }
+            diag_ok = diag_ok && dr && db && dr->ok == db->ok;
+            if (dr && db && dr->ok && db->ok)
+                worst_diag = std::max(worst_diag, std::fabs(db->energy - dr->energy) / std::fabs(dr->energy));
         }
         const Snapshot r = snap(wr), b = snap(wb);
         const auto* dev = wb.get<PhysicsB200::Device>();
-        std::printf("400-body disk with physical radii, 40 frames: %zu bodies left (reference %zu); device detections %lld, "
-                    "frames that ran the CPU merge %lld\n",
-                    b.pos.size() / 2, r.pos.size() / 2, dev->collision_checks, dev->collision_frames);
-        expect(r.pos.size() == b.pos.size() && r.pos.size() < 800, "same number of merges in both worlds");
+        std::printf("%d-body disk with %s radii, %d frames: %zu bodies left (reference %zu); device collision passes %lld, "
+                    "frames with a merge %lld, merges %lld; max |dE|/|E| of the frame diagnostics %.2e\n",
+                    n0, dense ? "puffy (Density 0.5)" : "physical", frames, b.pos.size() / 2, r.pos.size() / 2,
+                    dev->collision_checks, dev->collision_frames, dev->merges, worst_diag);
+        expect(r.pos.size() == b.pos.size() && (int)r.pos.size() / 2 < n0, "same bodies survive in both worlds");
         expect(bitwise(r.pos, b.pos) && bitwise(r.vel, b.vel) && bitwise(r.acc, b.acc), "state bit-identical after merges");
-        expect(dev->collision_checks == 40 && dev->collision_frames >= 1 && dev->collision_frames < 40,
-               "the reference's O(N^2) collision pass ran only on the frames with an overlap");
+        expect(diag_ok && worst_diag <= 2e-6, "frame diagnostics agree on every frame, merge frames included");
+        expect(dev->collision_checks == frames && dev->collision_frames >= 1 && dev->merges >= (long long)(n0 - r.pos.size() / 2),
+               "every frame's pass ran on the device; the reference's CPU pass never ran in the binding's world");
         PhysicsB200::shutdown(wb);
     }
     // ---- D: what the drop-in buys per frame (whole world.progress(): collisions, diagnostics, gravity,

@@ -355,3 +355,77 @@ int64_t orc_count_overlaps(int64_t n, const double* pos, const float* mass, cons
     }
     return count;
 }
+
+/* Collision::resolve in its default (merge) mode, src/systems/Collision.hpp:49-132, on flat arrays.
+ * radius[i] is what Collision::radius_of gives for body i on entry (:28-35: the Radius component, else
+ * the sphere of density[i]); density[i] is the Density component or Constants.hpp:34's 5510.
+ * In/out: pos, vel, mass, pinned, radius (the survivor's new values, :115-121,128-132). Out: alive[i] = 0
+ * for destructed bodies (:124-125), changed[i] = 1 for survivors whose components were rewritten (their
+ * Acceleration and PrevAcceleration become 0, :118-119). Returns the number of merges.
+ * Reproduced as they are: a row whose body dies keeps going with that body's snapshot — alive[i] is only
+ * looked at when the row starts (:76) — so later partners can still merge INTO the dead body (and vanish
+ * with it) or absorb its mass a second time. */
+int64_t orc_resolve_collisions(int64_t n, double* pos, double* vel, float* mass, uint8_t* pinned, double* radius,
+                               const double* density, uint8_t* alive, uint8_t* changed, int64_t* merge_log,
+                               int64_t merge_log_cap) {
+    const double pi = 3.141592653589793238462643383279502884; /* std::numbers::pi */
+    int64_t* idx = (int64_t*)malloc(sizeof(int64_t) * (size_t)(n > 0 ? n : 1));
+    int64_t m = 0, merges = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        alive[i] = 1;
+        changed[i] = 0;
+        if (!(isfinite(pos[2 * i]) && isfinite(pos[2 * i + 1]) && isfinite((double)mass[i]))) continue; /* :63-64 */
+        if (mass[i] <= 0.0f) continue;                                                                   /* :65 */
+        idx[m++] = i;
+    }
+    if (m >= 2) { /* :70 */
+        for (int64_t ii = 0; ii < m; ++ii) {
+            const int64_t a = idx[ii];
+            if (!alive[a]) continue; /* :76 */
+            for (int64_t jj = ii + 1; jj < m; ++jj) {
+                const int64_t b = idx[jj];
+                if (!alive[b]) continue; /* :78 */
+                const double dx = pos[2 * b] - pos[2 * a];
+                const double dy = pos[2 * b + 1] - pos[2 * a + 1];
+                const double rsum = radius[a] + radius[b];
+                const double dist2 = dx * dx + dy * dy;
+                if (dist2 > rsum * rsum) continue; /* :85 */
+                const int a_survives = (mass[a] >= mass[b]) || pinned[b]; /* :94 */
+                const int64_t s = a_survives ? a : b, d = a_survives ? b : a;
+                if (pinned[d] && pinned[s]) continue; /* :97-104 */
+                const double ms = (double)mass[s], md = (double)mass[d];
+                const double M = ms + md;                                   /* :107 */
+                const double px = ms * vel[2 * s] + md * vel[2 * d];        /* :108-109 */
+                const double py = ms * vel[2 * s + 1] + md * vel[2 * d + 1];
+                const double xx = (ms * pos[2 * s] + md * pos[2 * d]) / M;  /* :111-112 */
+                const double xy = (ms * pos[2 * s + 1] + md * pos[2 * d + 1]) / M;
+                mass[s] = (float)M;                                          /* :115,128 */
+                vel[2 * s] = px / M;                                         /* :110,116 */
+                vel[2 * s + 1] = py / M;
+                pos[2 * s] = xx;
+                pos[2 * s + 1] = xy;
+                pinned[s] = (pinned[s] || pinned[d]) ? 1 : 0;                /* :120,131 */
+                const double safe = (double)mass[s] > 1.0 ? (double)mass[s] : 1.0;
+                radius[s] = cbrt((3.0 * safe) / (4.0 * pi * density[s]));    /* :37-46,121,132 */
+                changed[s] = 1;
+                alive[d] = 0;                                                /* :124-125 */
+                if (merge_log && merges < merge_log_cap) { /* {survivor, absorbed} in the order of the merges */
+                    merge_log[2 * merges] = s;
+                    merge_log[2 * merges + 1] = d;
+                }
+                ++merges;
+            }
+        }
+    }
+    free(idx);
+    return merges;
+}
+
+/* Collision::radius_of without a Radius component, Collision.hpp:30-34 (libm cbrt, like the reference). */
+void orc_radius_from_mass(int64_t n, const float* mass, const double* density, double* radius) {
+    const double pi = 3.141592653589793238462643383279502884;
+    for (int64_t i = 0; i < n; ++i) {
+        const double safe = (double)mass[i] > 1.0 ? (double)mass[i] : 1.0;
+        radius[i] = cbrt((3.0 * safe) / (4.0 * pi * density[i]));
+    }
+}

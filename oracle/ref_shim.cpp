@@ -144,6 +144,51 @@ int64_t ref_collision_resolve(void* h, const double* radius) {
     return static_cast<int64_t>(rw->bodies.size());
 }
 
+// The same pass with everything it changed reported per ORIGINAL body (creation order of ref_load_bodies):
+// radius_in < 0 leaves the body without a Radius component (radius from mass and density, Collision.hpp:30-34),
+// density_in <= 0 leaves it without a Density component (Constants.hpp:34 applies). Outputs: alive flag and the
+// components of the bodies that are still alive; radius_out = Collision::radius_of after the pass.
+// visit_order[k] = original index of the k-th body the pass visits: flecs iterates table by table, and bodies
+// with and without a Radius (or Density) component live in different tables, so this is NOT creation order
+// in general. The caller restates the pass on the arrays permuted this way.
+int64_t ref_collision_resolve_full(void* h, const double* radius_in, const double* density_in, uint8_t* alive,
+                                   double* pos, double* vel, double* acc, float* mass, uint8_t* pinned,
+                                   double* radius_out, int64_t* visit_order) {
+    auto* rw = static_cast<RefWorld*>(h);
+    std::vector<flecs::entity> orig = rw->bodies;
+    for (size_t i = 0; i < orig.size(); ++i) {
+        if (radius_in[i] >= 0.0) orig[i].set<Radius>({radius_in[i]}); else orig[i].remove<Radius>();
+        if (density_in && density_in[i] > 0.0) orig[i].set<Density>({density_in[i]});
+    }
+    {
+        int64_t k = 0;
+        rw->w.each([&](const flecs::entity e, const Position&, const Velocity&, const Mass&, const Pinned&) {
+            for (size_t i = 0; i < orig.size(); ++i)
+                if (orig[i] == e) { visit_order[k++] = (int64_t)i; break; }
+        });
+    }
+    rw->w.defer_begin();
+    nbody::systems::Collision::resolve(rw->w);
+    rw->w.defer_end();
+    int64_t left = 0;
+    for (size_t i = 0; i < orig.size(); ++i) {
+        alive[i] = orig[i].is_alive() ? 1 : 0;
+        if (!alive[i]) continue;
+        ++left;
+        const auto* p = orig[i].get<Position>();
+        const auto* v = orig[i].get<Velocity>();
+        const auto* a = orig[i].get<Acceleration>();
+        pos[2 * i] = p->value.x; pos[2 * i + 1] = p->value.y;
+        vel[2 * i] = v->value.x; vel[2 * i + 1] = v->value.y;
+        acc[2 * i] = a->value.x; acc[2 * i + 1] = a->value.y;
+        mass[i] = orig[i].get<Mass>()->value;
+        pinned[i] = orig[i].get<Pinned>()->value ? 1 : 0;
+        radius_out[i] = nbody::systems::Collision::radius_of(orig[i], *orig[i].get<Mass>());
+    }
+    collect_bodies(rw);
+    return left;
+}
+
 // Built-in three-body seed with momentum zeroing (Physics.hpp:87-115). Radius{0} is
 // added afterwards so a later ref_progress() cannot merge bodies.
 int64_t ref_reset_scenario(void* h) {

@@ -25,14 +25,25 @@ __device__ __forceinline__ bool collide_input_ok(double x, double y, double z, f
     return finite_d(x) && finite_d(y) && finite_d(z) && m > 0.0f && m <= 3.4028234663852886e38f;
 }
 
-// result[0] = number of overlapping pairs, result[1] = min over them of i * n + j
+// result[0] = number of overlapping pairs, result[1] = min over them of i * n + j. With a pair sink
+// (nb_resolve_collisions) every overlapping pair's key i * n + j is also appended to pairs[] (result[2]
+// counts the appends; keys beyond pair_cap are dropped and the caller retries with a larger buffer).
+__device__ __forceinline__ void emit_pair(unsigned long long key, unsigned long long* pairs, unsigned long long pair_cap,
+                                          unsigned long long* result) {
+    if (!pairs) return;
+    const unsigned long long slot = atomicAdd(&result[2], 1ull);
+    if (slot < pair_cap) pairs[slot] = key;
+}
+
 template <bool D2>
 __global__ void __launch_bounds__(kOverlapThreads) overlap_kernel(const double* __restrict__ x0,
                                                                   const double* __restrict__ x1,
                                                                   const double* __restrict__ x2,
                                                                   const float* __restrict__ mass,
                                                                   const double* __restrict__ radius, long long n,
-                                                                  unsigned long long* result) {
+                                                                  unsigned long long* result,
+                                                                  unsigned long long* pairs = nullptr,
+                                                                  unsigned long long pair_cap = 0) {
     __shared__ double sx[kOverlapThreads], sy[kOverlapThreads], sz[kOverlapThreads], sr[kOverlapThreads];
     __shared__ unsigned char sok[kOverlapThreads];
     const long long i = blockIdx.x * (long long)kOverlapThreads + threadIdx.x;
@@ -78,6 +89,7 @@ __global__ void __launch_bounds__(kOverlapThreads) overlap_kernel(const double* 
                         ++count;
                         const unsigned long long key = (unsigned long long)i * (unsigned long long)n + (unsigned long long)j;
                         first = key < first ? key : first;
+                        emit_pair(key, pairs, pair_cap, result);
                     }
                 }
             }
@@ -188,7 +200,9 @@ __global__ void __launch_bounds__(256) grid_overlap_kernel(const double* __restr
                                                            const double* __restrict__ radius, long long n, GridSpec g,
                                                            const unsigned int* __restrict__ cell_start,
                                                            const unsigned int* __restrict__ sorted_idx,
-                                                           unsigned long long* result) {
+                                                           unsigned long long* result,
+                                                           unsigned long long* pairs = nullptr,
+                                                           unsigned long long pair_cap = 0) {
     const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     unsigned long long count = 0, first = ~0ull;
     if (i < n) {
@@ -219,6 +233,7 @@ __global__ void __launch_bounds__(256) grid_overlap_kernel(const double* __restr
                             ++count;
                             const unsigned long long key = (unsigned long long)i * (unsigned long long)n + (unsigned long long)j;
                             first = key < first ? key : first;
+                            emit_pair(key, pairs, pair_cap, result);
                         }
                     }
                 }
@@ -234,6 +249,46 @@ __global__ void __launch_bounds__(256) grid_overlap_kernel(const double* __restr
         atomicAdd(&result[0], count);
         atomicMin(&result[1], first);
     }
+}
+
+// ---- merge phase support (nb_resolve_collisions) --------------------------------------------------
+// The merges themselves are sequential (Collision.hpp:75-132: the survivor's position, mass and radius
+// change between pair tests) and are replayed on the host in the reference's order; the device keeps a
+// scratch copy of the CURRENT positions/radii/alive flags and answers, after every merge, "which living
+// bodies does the survivor's new state overlap?" — the only pairs whose outcome the merge can change.
+
+// hits[0 .. *n_hits) = every k != s with live[k] whose current state overlaps body s = (sx, sy, sr)
+__global__ void __launch_bounds__(256) collide_rescan_kernel(const double* __restrict__ cx, const double* __restrict__ cy,
+                                                             const double* __restrict__ cr,
+                                                             const unsigned char* __restrict__ live, long long n,
+                                                             long long s, double sx, double sy, double sr,
+                                                             unsigned int* hits, unsigned int* n_hits) {
+    const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (k >= n || k == s || !live[k]) return;
+    // (x_B - x_A)^2 and r_A + r_B do not depend on which of the two is A: one form serves both orders
+    const double dx = __dsub_rn(cx[k], sx);
+    const double dy = __dsub_rn(cy[k], sy);
+    const double rsum = __dadd_rn(sr, cr[k]);
+    const double dist2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+    if (!(dist2 > __dmul_rn(rsum, rsum))) hits[atomicAdd(n_hits, 1u)] = (unsigned int)k;
+}
+
+// scratch state after one merge: survivor s moved/grew, body d died (d < 0: nobody newly died)
+__global__ void collide_apply_kernel(double* cx, double* cy, double* cr, unsigned char* live, long long s, double sx,
+                                     double sy, double sr, long long d, unsigned int* n_hits) {
+    cx[s] = sx; cy[s] = sy; cr[s] = sr;
+    if (d >= 0) live[d] = 0;
+    *n_hits = 0;
+}
+
+// scratch copies for the merge phase: positions, radii (already on the device), live = passes the input filter
+__global__ void __launch_bounds__(256) collide_snapshot_kernel(const double* __restrict__ x0, const double* __restrict__ x1,
+                                                               const double* __restrict__ x2, const float* __restrict__ mass,
+                                                               long long n, double* cx, double* cy, unsigned char* live) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    cx[i] = x0[i]; cy[i] = x1[i];
+    live[i] = collide_input_ok(x0[i], x1[i], x2[i], mass[i]) ? 1 : 0;
 }
 
 }  // namespace nb

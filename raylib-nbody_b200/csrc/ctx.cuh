@@ -72,6 +72,9 @@ struct nb_ctx {
     void* collide_scratch = nullptr;    // nb_count_overlaps: radii, grid arrays, scan temp
     size_t collide_bytes = 0;
     long long overlap_grid_calls = 0;   // calls that took the O(N) grid broad phase
+    void* merge_scratch = nullptr;      // nb_resolve_collisions: pair sink, current positions, hit list
+    size_t merge_bytes = 0;
+    long long merge_passes = 0;         // calls that found an overlap and replayed merges
     size_t staging_bytes = 0;
 
     // ---- the reference's solver switch (Physics.hpp:212): Barnes-Hut above bh_threshold bodies ----

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <set>
 #include <string>
 
 #include "bh.cuh"
@@ -439,6 +440,7 @@ extern "C" void nb_destroy(nb_ctx* c) {
     cudaFree(c->l2_scratch);
     cudaFree(c->collide_scratch);
     cudaFree(c->bh_scratch);
+    cudaFree(c->merge_scratch);
     if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
     cudaFree(c->totals);
     cudaFreeHost(c->h_totals);
@@ -1344,13 +1346,10 @@ GridSpec plan_grid(int dim, const double lo[3], const double hi[3], double r_max
 
 }  // namespace
 
-extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair) {
-    if (!c || !n_overlaps) return fail(NB_ERR_INVALID, "nb_count_overlaps: null");
-    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_count_overlaps: single-GPU contexts only (FP64 positions are not replicated)");
-    *n_overlaps = 0;
-    if (first_pair) first_pair[0] = first_pair[1] = -1;
-    if (c->n < 2) return NB_OK;  // Collision.hpp:70
-    if (!radius) return fail(NB_ERR_INVALID, "nb_count_overlaps: null radius array");
+// Detection over all pairs (all-pairs sweep or grid broad phase). d_pairs (optional, device): sink for the
+// overlapping pairs' keys i * n + j; *n_emitted = how many the kernels tried to append.
+static int overlaps_impl(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair,
+                         unsigned long long* d_pairs, unsigned long long pair_cap, unsigned long long* n_emitted) {
     NB_CUDA(cudaSetDevice(c->device));
     const long long n = c->n;
     const StateView s = c->view();
@@ -1366,7 +1365,7 @@ extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_ove
     unsigned long long* d_bounds = reinterpret_cast<unsigned long long*>(base);
     unsigned long long* d_res = d_bounds + 6;
     double* d_radius = reinterpret_cast<double*>(base + off_radius);
-    const unsigned long long init[8] = {~0ull, 0ull, ~0ull, 0ull, ~0ull, 0ull, 0ull, ~0ull};
+    const unsigned long long init[9] = {~0ull, 0ull, ~0ull, 0ull, ~0ull, 0ull, 0ull, ~0ull, 0ull};
     NB_CUDA(cudaMemcpyAsync(d_bounds, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
     NB_CUDA(cudaMemcpyAsync(d_radius, radius, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
 
@@ -1413,20 +1412,20 @@ extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_ove
         grid_bin_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, g, nullptr, cell_start,
                                                                   cell_fill, sorted_idx);
         grid_overlap_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, g,
-                                                                      cell_start, sorted_idx, d_res);
+                                                                      cell_start, sorted_idx, d_res, d_pairs, pair_cap);
         c->kernel_launches += 4;
         c->overlap_grid_calls++;
     } else {
         if (c->dim == 2)
             overlap_kernel<true><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res);
+                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res, d_pairs, pair_cap);
         else
             overlap_kernel<false><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res);
+                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res, d_pairs, pair_cap);
         c->kernel_launches++;
     }
     NB_CUDA(cudaGetLastError());
-    unsigned long long res[2];
+    unsigned long long res[3];
     NB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     *n_overlaps = (int64_t)res[0];
@@ -1434,6 +1433,170 @@ extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_ove
         first_pair[0] = (int64_t)(res[1] / (unsigned long long)n);
         first_pair[1] = (int64_t)(res[1] % (unsigned long long)n);
     }
+    if (n_emitted) *n_emitted = res[2];
+    return NB_OK;
+}
+
+extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair) {
+    if (!c || !n_overlaps) return fail(NB_ERR_INVALID, "nb_count_overlaps: null");
+    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_count_overlaps: single-GPU contexts only (FP64 positions are not replicated)");
+    *n_overlaps = 0;
+    if (first_pair) first_pair[0] = first_pair[1] = -1;
+    if (c->n < 2) return NB_OK;  // Collision.hpp:70
+    if (!radius) return fail(NB_ERR_INVALID, "nb_count_overlaps: null radius array");
+    return overlaps_impl(c, radius, n_overlaps, first_pair, nullptr, 0, nullptr);
+}
+
+// Collision::resolve in its default merge mode (Collision.hpp:49-132). The pair tests run on the device; the
+// merges are replayed on the host in the reference's visiting order as an event queue:
+//   * pairs whose two bodies are untouched so far behave as the initial detection says;
+//   * every merge changes exactly one snapshot (the survivor's): the device re-tests that body against all
+//     living bodies (collide_rescan_kernel) and the hits that still lie AHEAD in the (i, j) order are queued;
+//   * an event is re-tested with the current snapshots when its turn comes.
+// Any pair that overlaps when the reference would test it was detected either initially or by the rescan that
+// followed the last change of one of its bodies, so the replay performs exactly the reference's merges.
+extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const double* density, int64_t* n_merges,
+                                     uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
+                                     uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap) {
+    if (!c || !n_merges || !alive || !changed) return fail(NB_ERR_INVALID, "nb_resolve_collisions: null");
+    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_resolve_collisions: single-GPU contexts only");
+    if (c->dim != 2) return fail(NB_ERR_INVALID, "nb_resolve_collisions: the reference's collision pass is 2-D (nb_upload)");
+    *n_merges = 0;
+    const long long n = c->n;
+    for (long long i = 0; i < n; ++i) { alive[i] = 1; changed[i] = 0; }
+    if (n < 2) return NB_OK;  // Collision.hpp:70
+    if (!radius || !density || !pos_xy || !vel_xy || !mass || !pinned || !radius_out)
+        return fail(NB_ERR_INVALID, "nb_resolve_collisions: null array");
+    NB_CUDA(cudaSetDevice(c->device));
+
+    // scratch of the merge phase: pair sink | cx | cy | hits | live | hit counter
+    unsigned long long pair_cap = (unsigned long long)std::max<long long>(4 * n, 1 << 16);
+    int64_t overlaps = 0;
+    unsigned long long emitted = 0;
+    size_t off_cx = 0, off_cy = 0, off_hits = 0, off_live = 0, off_cnt = 0;
+    for (;;) {
+        off_cx = align256(sizeof(unsigned long long) * pair_cap);
+        off_cy = off_cx + align256(sizeof(double) * (size_t)n);
+        off_hits = off_cy + align256(sizeof(double) * (size_t)n);
+        off_live = off_hits + align256(sizeof(unsigned int) * (size_t)n);
+        off_cnt = off_live + align256((size_t)n);
+        const size_t total = off_cnt + 256;
+        if (total > c->merge_bytes) {
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            if (c->merge_scratch) cudaFree(c->merge_scratch);
+            c->merge_scratch = nullptr;
+            c->merge_bytes = 0;
+            NB_CUDA(cudaMalloc(&c->merge_scratch, total));
+            c->merge_bytes = total;
+        }
+        NB_TRY(overlaps_impl(c, radius, &overlaps, nullptr, static_cast<unsigned long long*>(c->merge_scratch), pair_cap,
+                             &emitted));
+        if (emitted <= pair_cap) break;
+        pair_cap = emitted + 1024;  // more overlapping pairs than the sink held: once more with room for all
+    }
+    if (overlaps == 0) return NB_OK;  // the common frame: resolve() changes nothing
+
+    char* mb = static_cast<char*>(c->merge_scratch);
+    double* d_cx = reinterpret_cast<double*>(mb + off_cx);
+    double* d_cy = reinterpret_cast<double*>(mb + off_cy);
+    unsigned int* d_hits = reinterpret_cast<unsigned int*>(mb + off_hits);
+    unsigned char* d_live = reinterpret_cast<unsigned char*>(mb + off_live);
+    unsigned int* d_cnt = reinterpret_cast<unsigned int*>(mb + off_cnt);
+    double* d_cr = reinterpret_cast<double*>(static_cast<char*>(c->collide_scratch) + 256);  // the radii overlaps_impl staged
+
+    // host snapshots (Collision.hpp:51-67): everything the merges read and write
+    std::vector<unsigned long long> keys((size_t)emitted);
+    NB_CUDA(cudaMemcpyAsync(keys.data(), c->merge_scratch, sizeof(unsigned long long) * (size_t)emitted, cudaMemcpyDeviceToHost,
+                            c->stream));
+    const StateView sv = c->view();
+    collide_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], c->mass, n, d_cx, d_cy, d_live);
+    NB_CUDA(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned int), c->stream));
+    c->kernel_launches++;
+    std::vector<double> hp(2 * (size_t)n), hv(2 * (size_t)n), hr(radius, radius + n);
+    std::vector<float> hm((size_t)n);
+    std::vector<uint8_t> hpin((size_t)n), hlive((size_t)n);
+    NB_TRY(download_dim(c, hp.data(), hv.data(), nullptr, 2));
+    NB_CUDA(cudaMemcpyAsync(hm.data(), c->mass, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(hpin.data(), c->pinned, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(hlive.data(), d_live, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+
+    std::set<unsigned long long> events(keys.begin(), keys.end());
+    std::vector<unsigned int> hits((size_t)n);
+    const unsigned long long un = (unsigned long long)n;
+    const double pi = 3.141592653589793238462643383279502884;  // std::numbers::pi
+    long long cur_row = -1;
+    bool row_alive = false;
+    int64_t merges = 0;
+    while (!events.empty()) {
+        const unsigned long long key = *events.begin();
+        events.erase(events.begin());
+        const long long a = (long long)(key / un), b = (long long)(key % un);
+        if (a != cur_row) {  // alive[i] is looked at when row i starts and not again (:76)
+            cur_row = a;
+            row_alive = alive[a] != 0;
+        }
+        if (!row_alive || !alive[b]) continue;  // :76, :78
+        const double dx = hp[2 * b] - hp[2 * a];
+        const double dy = hp[2 * b + 1] - hp[2 * a + 1];
+        const double rsum = hr[a] + hr[b];
+        const double dist2 = dx * dx + dy * dy;
+        if (dist2 > rsum * rsum) continue;  // :85, with the snapshots as they are NOW
+        const bool a_survives = (hm[a] >= hm[b]) || hpin[b];  // :94
+        const long long sv_i = a_survives ? a : b, dd = a_survives ? b : a;
+        if (hpin[dd] && hpin[sv_i]) continue;  // :97-104
+        const double ms = (double)hm[sv_i], md = (double)hm[dd];
+        const double M = ms + md;                                            // :107
+        const double px = ms * hv[2 * sv_i] + md * hv[2 * dd];               // :108-109
+        const double py = ms * hv[2 * sv_i + 1] + md * hv[2 * dd + 1];
+        const double xx = (ms * hp[2 * sv_i] + md * hp[2 * dd]) / M;         // :111-112
+        const double xy = (ms * hp[2 * sv_i + 1] + md * hp[2 * dd + 1]) / M;
+        hm[sv_i] = (float)M;                                                 // :115,128
+        hv[2 * sv_i] = px / M;                                               // :110,116
+        hv[2 * sv_i + 1] = py / M;
+        hp[2 * sv_i] = xx;
+        hp[2 * sv_i + 1] = xy;
+        hpin[sv_i] = (hpin[sv_i] || hpin[dd]) ? 1 : 0;                       // :120,131
+        hr[sv_i] = std::cbrt((3.0 * std::max(1.0, (double)hm[sv_i])) / (4.0 * pi * density[sv_i]));  // :37-46,132
+        changed[sv_i] = 1;
+        const bool newly_dead = alive[dd] != 0;
+        alive[dd] = 0;                                                       // :124-125
+        if (merge_log && merges < merge_log_cap) {
+            merge_log[2 * merges] = sv_i;
+            merge_log[2 * merges + 1] = dd;
+        }
+        ++merges;
+        // which living bodies does the survivor's new state reach?
+        collide_apply_kernel<<<1, 1, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, sv_i, xx, xy, hr[sv_i], newly_dead ? dd : -1, d_cnt);
+        collide_rescan_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, n, sv_i, xx, xy, hr[sv_i],
+                                                                       d_hits, d_cnt);
+        c->kernel_launches += 2;
+        unsigned int n_hits = 0;
+        NB_CUDA(cudaMemcpyAsync(&n_hits, d_cnt, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (n_hits) {
+            NB_CUDA(cudaMemcpyAsync(hits.data(), d_hits, sizeof(unsigned int) * n_hits, cudaMemcpyDeviceToHost, c->stream));
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            for (unsigned int h = 0; h < n_hits; ++h) {
+                const unsigned long long k = hits[h];
+                const unsigned long long lo = std::min<unsigned long long>(k, (unsigned long long)sv_i);
+                const unsigned long long hi = std::max<unsigned long long>(k, (unsigned long long)sv_i);
+                const unsigned long long nk = lo * un + hi;
+                if (nk > key) events.insert(nk);  // only tests the reference has not made yet
+            }
+        }
+    }
+    NB_CUDA(cudaGetLastError());
+    for (long long i = 0; i < n; ++i) {
+        if (!changed[i]) continue;
+        pos_xy[2 * i] = hp[2 * i]; pos_xy[2 * i + 1] = hp[2 * i + 1];
+        vel_xy[2 * i] = hv[2 * i]; vel_xy[2 * i + 1] = hv[2 * i + 1];
+        mass[i] = hm[i];
+        pinned[i] = hpin[i];
+        radius_out[i] = hr[i];
+    }
+    *n_merges = merges;
+    c->merge_passes++;
     return NB_OK;
 }
 

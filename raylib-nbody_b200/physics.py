@@ -57,12 +57,13 @@ class Diagnostics:
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
-           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps",
+           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
 SOLVER_DIRECT, SOLVER_REFERENCE = 0, 1
+BODY_DENSITY = 5510.0  # Constants.hpp:34
 REF_BH_THRESHOLD, REF_BH_THETA = 100, 0.5  # Constants.hpp:90-91
 
 _lib = None
@@ -95,6 +96,8 @@ def load_library(path=LIB_PATH):
     L.nb_download3.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_download_state.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
     L.nb_count_overlaps.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.nb_resolve_collisions.argtypes = [C.c_void_p, _dp, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8),
+                                        _dp, _dp, C.POINTER(C.c_float), C.POINTER(C.c_uint8), _dp, C.POINTER(C.c_int64), C.c_int64]
     L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_default_config.argtypes = [C.POINTER(Config)]
@@ -295,6 +298,35 @@ class Physics:
         cnt, first = C.c_int64(), (C.c_int64 * 2)()
         _check(self._L.nb_count_overlaps(self._h, r.ctypes.data_as(_dp), C.byref(cnt), first))
         return cnt.value, ((first[0], first[1]) if cnt.value else None)
+
+    def resolve_collisions(self, radius, density=None, with_log=False):
+        """Collision::resolve, merge mode (Collision.hpp:49-132). Returns (n_merges, alive, changed, pos, vel, mass,
+        pinned, radius): alive[i] = 0 where the reference destructs the body; for changed[i] = 1 the survivor's
+        new components (other rows of the arrays are zero). The device state is left as it is."""
+        n = self.num_bodies()
+        r = np.ascontiguousarray(radius, dtype=np.float64)
+        rho = np.full(n, BODY_DENSITY) if density is None else np.ascontiguousarray(density, dtype=np.float64)
+        if r.shape != (n,) or rho.shape != (n,):
+            raise ValueError("radius and density must have one entry per body")
+        alive, changed = np.ones(n, np.uint8), np.zeros(n, np.uint8)
+        pos, vel = np.zeros((n, 2)), np.zeros((n, 2))
+        mass, pinned, rout = np.zeros(n, np.float32), np.zeros(n, np.uint8), np.zeros(n)
+        k = C.c_int64()
+        u8 = C.POINTER(C.c_uint8)
+        _check(self._L.nb_resolve_collisions(self._h, r.ctypes.data_as(_dp), rho.ctypes.data_as(_dp), C.byref(k),
+                                             alive.ctypes.data_as(u8), changed.ctypes.data_as(u8), pos.ctypes.data_as(_dp),
+                                             vel.ctypes.data_as(_dp), mass.ctypes.data_as(C.POINTER(C.c_float)),
+                                             pinned.ctypes.data_as(u8), rout.ctypes.data_as(_dp), None, 0))
+        if with_log:  # the merges in the reference's order, {survivor, absorbed}
+            log = np.zeros((max(k.value, 1), 2), np.int64)
+            k2 = C.c_int64()
+            _check(self._L.nb_resolve_collisions(self._h, r.ctypes.data_as(_dp), rho.ctypes.data_as(_dp), C.byref(k2),
+                                                 alive.ctypes.data_as(u8), changed.ctypes.data_as(u8), pos.ctypes.data_as(_dp),
+                                                 vel.ctypes.data_as(_dp), mass.ctypes.data_as(C.POINTER(C.c_float)),
+                                                 pinned.ctypes.data_as(u8), rout.ctypes.data_as(_dp),
+                                                 log.ctypes.data_as(C.POINTER(C.c_int64)), log.shape[0]))
+            return k.value, alive, changed, pos, vel, mass, pinned, rout, log[:k.value]
+        return k.value, alive, changed, pos, vel, mass, pinned, rout
 
     def download_state(self):
         """(pos, vel, acc, acc_prev): the four DVec2 components of Components.hpp:10-21."""
