@@ -38,7 +38,13 @@ namespace cg = cooperative_groups;
 
 constexpr int kBhMaxLevels = 320;  // a float half-size underflows to 0 after < 300 halvings
 constexpr int kBhBuildThreads = 256;
-constexpr int kBhWalkThreads = 128;
+#ifndef NB_BH_WALK_NT
+#define NB_BH_WALK_NT 128
+#endif
+#ifndef NB_BH_WALK_MINB
+#define NB_BH_WALK_MINB 1
+#endif
+constexpr int kBhWalkThreads = NB_BH_WALK_NT;
 constexpr int kBhKeyLevels = 16;   // tree levels in the Z-order key
 constexpr int kBhHistCells = 4096; // levels with at most this many new cells count bodies per CTA first
 
@@ -282,7 +288,7 @@ __global__ void __launch_bounds__(kBhBuildThreads) bh_build_kernel(StateView s, 
 // One walk per body (Physics.hpp:224-230 + SpatialPartition.hpp:63-106). order[]: body rows in Z-order.
 // visits (optional): per-launch totals {cells popped, terms added, exact re-evaluations of the accept test}.
 template <bool STATS>
-__global__ void __launch_bounds__(kBhWalkThreads) bh_walk_kernel(StateView s, BhTree t, const int* __restrict__ order,
+__global__ void __launch_bounds__(kBhWalkThreads, NB_BH_WALK_MINB) bh_walk_kernel(StateView s, BhTree t, const int* __restrict__ order,
                                                                  double g, float softening, float theta_f,
                                                                  unsigned long long* visits) {
     const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
