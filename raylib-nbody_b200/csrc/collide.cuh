@@ -257,28 +257,30 @@ __global__ void __launch_bounds__(256) grid_overlap_kernel(const double* __restr
 // scratch copy of the CURRENT positions/radii/alive flags and answers, after every merge, "which living
 // bodies does the survivor's new state overlap?" — the only pairs whose outcome the merge can change.
 
-// hits[0 .. *n_hits) = every k != s with live[k] whose current state overlaps body s = (sx, sy, sr)
-__global__ void __launch_bounds__(256) collide_rescan_kernel(const double* __restrict__ cx, const double* __restrict__ cy,
-                                                             const double* __restrict__ cr,
-                                                             const unsigned char* __restrict__ live, long long n,
-                                                             long long s, double sx, double sy, double sr,
-                                                             unsigned int* hits, unsigned int* n_hits) {
+// One launch per merge: record the merge in the scratch state (survivor s moved/grew, body d died; d < 0: nobody
+// newly died) and report every living k != s whose current state overlaps the survivor's new one.
+// out[0] is a running total of hits over the whole replay (base = its value before this launch), the hits of
+// this launch land in out[1 + (slot - base)]: no counter reset, no second launch, one readback.
+__global__ void __launch_bounds__(256) collide_rescan_kernel(double* cx, double* cy, double* cr, unsigned char* live,
+                                                             long long n, long long s, double sx, double sy, double sr,
+                                                             long long d, unsigned int* out, unsigned int base) {
     const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (k >= n || k == s || !live[k]) return;
+    if (k >= n) return;
+    if (k == s) {  // every other thread reads its own row only
+        cx[s] = sx; cy[s] = sy; cr[s] = sr;
+        return;
+    }
+    if (k == d) {
+        live[d] = 0;
+        return;
+    }
+    if (!live[k]) return;
     // (x_B - x_A)^2 and r_A + r_B do not depend on which of the two is A: one form serves both orders
     const double dx = __dsub_rn(cx[k], sx);
     const double dy = __dsub_rn(cy[k], sy);
     const double rsum = __dadd_rn(sr, cr[k]);
     const double dist2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    if (!(dist2 > __dmul_rn(rsum, rsum))) hits[atomicAdd(n_hits, 1u)] = (unsigned int)k;
-}
-
-// scratch state after one merge: survivor s moved/grew, body d died (d < 0: nobody newly died)
-__global__ void collide_apply_kernel(double* cx, double* cy, double* cr, unsigned char* live, long long s, double sx,
-                                     double sy, double sr, long long d, unsigned int* n_hits) {
-    cx[s] = sx; cy[s] = sy; cr[s] = sr;
-    if (d >= 0) live[d] = 0;
-    *n_hits = 0;
+    if (!(dist2 > __dmul_rn(rsum, rsum))) out[1 + (atomicAdd(&out[0], 1u) - base)] = (unsigned int)k;
 }
 
 // scratch copies for the merge phase: positions, radii (already on the device), live = passes the input filter

@@ -74,6 +74,7 @@ struct nb_ctx {
     long long overlap_grid_calls = 0;   // calls that took the O(N) grid broad phase
     void* merge_scratch = nullptr;      // nb_resolve_collisions: pair sink, current positions, hit list
     size_t merge_bytes = 0;
+    unsigned int* h_merge = nullptr;    // pinned: hit count + first hits of a rescan
     long long merge_passes = 0;         // calls that found an overlap and replayed merges
     size_t staging_bytes = 0;
 

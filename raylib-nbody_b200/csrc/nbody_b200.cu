@@ -441,6 +441,7 @@ extern "C" void nb_destroy(nb_ctx* c) {
     cudaFree(c->collide_scratch);
     cudaFree(c->bh_scratch);
     cudaFree(c->merge_scratch);
+    if (c->h_merge) cudaFreeHost(c->h_merge);
     if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
     cudaFree(c->totals);
     cudaFreeHost(c->h_totals);
@@ -1473,12 +1474,13 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
     unsigned long long pair_cap = (unsigned long long)std::max<long long>(4 * n, 1 << 16);
     int64_t overlaps = 0;
     unsigned long long emitted = 0;
+    constexpr long long kMergeFirstHits = 64;  // count + this many hits ride in the first readback
     size_t off_cx = 0, off_cy = 0, off_hits = 0, off_live = 0, off_cnt = 0;
     for (;;) {
         off_cx = align256(sizeof(unsigned long long) * pair_cap);
         off_cy = off_cx + align256(sizeof(double) * (size_t)n);
         off_hits = off_cy + align256(sizeof(double) * (size_t)n);
-        off_live = off_hits + align256(sizeof(unsigned int) * (size_t)n);
+        off_live = off_hits + align256(sizeof(unsigned int) * ((size_t)n + 1));
         off_cnt = off_live + align256((size_t)n);
         const size_t total = off_cnt + 256;
         if (total > c->merge_bytes) {
@@ -1499,9 +1501,8 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
     char* mb = static_cast<char*>(c->merge_scratch);
     double* d_cx = reinterpret_cast<double*>(mb + off_cx);
     double* d_cy = reinterpret_cast<double*>(mb + off_cy);
-    unsigned int* d_hits = reinterpret_cast<unsigned int*>(mb + off_hits);
+    unsigned int* d_hits = reinterpret_cast<unsigned int*>(mb + off_hits);  // [0]: running hit total, [1..]: this launch's hits
     unsigned char* d_live = reinterpret_cast<unsigned char*>(mb + off_live);
-    unsigned int* d_cnt = reinterpret_cast<unsigned int*>(mb + off_cnt);
     double* d_cr = reinterpret_cast<double*>(static_cast<char*>(c->collide_scratch) + 256);  // the radii overlaps_impl staged
 
     // host snapshots (Collision.hpp:51-67): everything the merges read and write
@@ -1510,8 +1511,9 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
                             c->stream));
     const StateView sv = c->view();
     collide_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], c->mass, n, d_cx, d_cy, d_live);
-    NB_CUDA(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned int), c->stream));
+    NB_CUDA(cudaMemsetAsync(d_hits, 0, sizeof(unsigned int), c->stream));
     c->kernel_launches++;
+    if (!c->h_merge) NB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_merge), sizeof(unsigned int) * kMergeFirstHits));
     std::vector<double> hp(2 * (size_t)n), hv(2 * (size_t)n), hr(radius, radius + n);
     std::vector<float> hm((size_t)n);
     std::vector<uint8_t> hpin((size_t)n), hlive((size_t)n);
@@ -1528,6 +1530,7 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
     long long cur_row = -1;
     bool row_alive = false;
     int64_t merges = 0;
+    unsigned int hit_base = 0;
     while (!events.empty()) {
         const unsigned long long key = *events.begin();
         events.erase(events.begin());
@@ -1566,24 +1569,28 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
             merge_log[2 * merges + 1] = dd;
         }
         ++merges;
-        // which living bodies does the survivor's new state reach?
-        collide_apply_kernel<<<1, 1, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, sv_i, xx, xy, hr[sv_i], newly_dead ? dd : -1, d_cnt);
+        // which living bodies does the survivor's new state reach? One launch, one readback of the count and
+        // the first hits into pinned memory; the (rare) long hit lists take a second copy.
         collide_rescan_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, n, sv_i, xx, xy, hr[sv_i],
-                                                                       d_hits, d_cnt);
-        c->kernel_launches += 2;
-        unsigned int n_hits = 0;
-        NB_CUDA(cudaMemcpyAsync(&n_hits, d_cnt, sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+                                                                       newly_dead ? dd : -1, d_hits, hit_base);
+        c->kernel_launches++;
+        const size_t first = (size_t)std::min<long long>(kMergeFirstHits, n + 1);
+        NB_CUDA(cudaMemcpyAsync(c->h_merge, d_hits, sizeof(unsigned int) * first, cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        if (n_hits) {
-            NB_CUDA(cudaMemcpyAsync(hits.data(), d_hits, sizeof(unsigned int) * n_hits, cudaMemcpyDeviceToHost, c->stream));
+        const unsigned int n_hits = c->h_merge[0] - hit_base;
+        hit_base = c->h_merge[0];
+        const unsigned int* hit = c->h_merge + 1;
+        if ((size_t)n_hits + 1 > first) {
+            NB_CUDA(cudaMemcpyAsync(hits.data(), d_hits + 1, sizeof(unsigned int) * n_hits, cudaMemcpyDeviceToHost, c->stream));
             NB_CUDA(cudaStreamSynchronize(c->stream));
-            for (unsigned int h = 0; h < n_hits; ++h) {
-                const unsigned long long k = hits[h];
-                const unsigned long long lo = std::min<unsigned long long>(k, (unsigned long long)sv_i);
-                const unsigned long long hi = std::max<unsigned long long>(k, (unsigned long long)sv_i);
-                const unsigned long long nk = lo * un + hi;
-                if (nk > key) events.insert(nk);  // only tests the reference has not made yet
-            }
+            hit = hits.data();
+        }
+        for (unsigned int h = 0; h < n_hits; ++h) {
+            const unsigned long long k = hit[h];
+            const unsigned long long lo = std::min<unsigned long long>(k, (unsigned long long)sv_i);
+            const unsigned long long hi = std::max<unsigned long long>(k, (unsigned long long)sv_i);
+            const unsigned long long nk = lo * un + hi;
+            if (nk > key) events.insert(nk);  // only tests the reference has not made yet
         }
     }
     NB_CUDA(cudaGetLastError());
