@@ -178,3 +178,38 @@ def test_full_size_2e20_bitexact(pkg, ph, oracle_lib):
     ph.step(50.0, 5)
     p, v, a = ph.download()
     assert np.isfinite(p).all() and np.isfinite(v).all() and ph.solver_info()["passes"] == 1 + 6
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5])
+def test_tiny_worlds_on_the_tree_side(pkg, ph, oracle_lib, n):
+    """bh_threshold = 0 sends even a single body through the tree (root leaf, no partner)."""
+    rng = np.random.default_rng(n)
+    pos = (rng.standard_normal((n, 2)) * 1e8).astype(np.float32).astype(np.float64)
+    vel = np.zeros((n, 2))
+    mass = rng.uniform(1e22, 1e24, n).astype(np.float32)
+    ph.set_solver(pkg.SOLVER_REFERENCE, 0, 0.5)
+    ph.set_config(softening=0.0)  # epsilon = 0 is allowed (Physics.hpp:186)
+    acc = gravity(ph, pos, vel, mass)
+    assert np.array_equal(acc, oracle_lib.bh_gravity(pos, vel, mass, softening=0.0))
+    assert ph.solver_info()["bodies"] == n and (n > 1 or not acc.any())
+
+
+def test_all_pinned_and_all_filtered(pkg, ph, oracle_lib):
+    pos, vel, mass = pkg.scenarios.uniform_disk(300, seed=12)
+    pinned = np.ones(300, np.uint8)
+    acc = gravity(ph, pos, vel, mass, pinned)
+    assert not acc.any() and ph.solver_info()["passes"] == 1  # the tree is built, nobody walks it (Physics.hpp:225)
+    # nothing passes the gather filter: compute_gravity returns before touching anything (Physics.hpp:208)
+    ph.upload(pos, vel, np.zeros(300, np.float32))
+    ph.compute_gravity()
+    assert not ph.download()[2].any()
+
+
+def test_direct_solver_is_the_default_and_unchanged_by_the_threshold(pkg, oracle_lib):
+    pos, vel, mass = pkg.scenarios.uniform_disk(400, seed=5)
+    p = pkg.Physics(0)
+    assert p.get_solver()[0] == pkg.SOLVER_DIRECT
+    p.upload(pos, vel, mass)
+    p.compute_gravity()
+    assert np.array_equal(p.download()[2], oracle_lib.compute_gravity(pos, vel, mass))  # 400 <= 512: FP64-exact direct sum
+    p.close()

@@ -121,3 +121,30 @@ def test_against_live_reference(oracle_lib, ob):
             assert np.array_equal(P, p, equal_nan=True) and np.array_equal(V, v, equal_nan=True)
             assert np.array_equal(A, a, equal_nan=True)
     r.close()
+
+
+def test_tiny_and_degenerate_worlds_against_live_reference(oracle_lib, ob):
+    if not ob.have_reference():
+        pytest.skip("oracle/_ref/libnbref.so not present (no /root/reference on this machine)")
+    rng = np.random.default_rng(17)
+    r = ob.Reference()
+    for n in (1, 2, 3, 5, 40):
+        pos = (rng.standard_normal((n, 2)) * 1e8).astype(np.float32).astype(np.float64)
+        vel = np.zeros((n, 2))
+        mass = rng.uniform(1e22, 1e24, n).astype(np.float32)
+        for pinned in (None, np.ones(n, np.uint8)):
+            r.set_config(softening=0.0)
+            r.set_solver(0, 0.5)
+            r.load_bodies(pos, vel, mass, pinned)
+            r.compute_gravity()
+            assert np.array_equal(r.read_bodies()[2], oracle_lib.bh_gravity(pos, vel, mass, pinned, softening=0.0))
+    # all bodies on one vertical line: the root square comes from the y extent alone; and one on a single point's
+    # neighbourhood with a huge offset (float spacing >> separation in double)
+    n = 64
+    pos = np.zeros((n, 2)); pos[:, 1] = np.linspace(-1e8, 1e8, n)
+    pos = pos.astype(np.float32).astype(np.float64)
+    r.set_solver(10, 0.5)
+    r.load_bodies(pos, np.zeros((n, 2)), np.full(n, 1e23, np.float32))
+    r.compute_gravity()
+    assert np.array_equal(r.read_bodies()[2], oracle_lib.bh_gravity(pos, np.zeros((n, 2)), np.full(n, 1e23, np.float32)))
+    r.close()
