@@ -1,16 +1,16 @@
-// collide.cuh — detection phase of the reference's collision pass on the device.
+// collide.cuh — the pair tests of the reference's collision pass on the device.
 //
 // Collision::resolve (src/systems/Collision.hpp:49-203) snapshots every body that passes its
 // input filter (finite position, finite mass > 0, :63-65) and walks all pairs i < j testing
 //     dx = xj - xi; dy = yj - yi; rsum = ri + rj; dist2 = dx*dx + dy*dy;
 //     if (dist2 > rsum * rsum) continue;            // no overlap            (:76-84)
-// before it merges anything. When no pair overlaps the whole pass is a no-op — the common frame,
-// and an O(N^2) FP64 loop on one host core (22 ms at N = 4096, ~25 min at 2^20). This kernel
-// evaluates exactly that predicate, in the reference's operation order with non-contracted FP64
-// arithmetic, for all pairs i < j, and returns the number of overlapping pairs and the first one
-// in the reference's visiting order. The caller (include/reference_side/PhysicsB200.hpp) runs the
-// reference's own resolve only on frames where the count is non-zero, so merge semantics stay
-// the reference's, bit for bit.
+// merging the pairs that overlap as it goes. When no pair overlaps the whole pass is a no-op — the
+// common frame, and an O(N^2) FP64 loop on one host core (22 ms at N = 4096, ~25 min at 2^20). The
+// kernels here evaluate exactly that predicate, in the reference's operation order with
+// non-contracted FP64 arithmetic: over all pairs (count, first pair, optionally the list of pairs:
+// nb_count_overlaps and the first step of nb_resolve_collisions), and for one changed body against
+// all others (the rescan after every merge of nb_resolve_collisions, which replays the merges in the
+// reference's order on the host; see the comment above that function in nbody_b200.cu).
 //
 // FP64-pipe bound: 8 FP64 operations per pair; triangular sweep (j-tiles at or after the
 // target's own tile).
