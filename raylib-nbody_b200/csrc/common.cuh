@@ -31,7 +31,7 @@ constexpr int kStages = NB_STAGES;         // TMA bulk-copy ring depth (8 KB sta
 constexpr int kFlushChunk = 64;           // FP32 partial sums are folded into FP64 every 64 sources
 constexpr int kExtentSlots = 4;           // rotating max|x| slots, see scale_for()
 constexpr int kHeadroomLog2 = 17;         // scaled |x| < 2^17 when packed; r^6 stays finite up to 2^19
-constexpr int kMaxSegments = 16;          // j-split factor upper bound
+constexpr int kMaxSegments = 64;          // j-split factor upper bound
 constexpr float kFarPacked = 1152921504606846976.0f;  // 2^60: packed x of non-attracting rows
 constexpr int kDiagValues = 12;           // KE, PE, Px,Py,Pz, Cx,Cy,Cz, M, nonfinite, pad, pad
 

@@ -195,8 +195,10 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
             // profiles/r01_time_modes.txt), or (work / units) when the grid cannot fill the slots
             const double per_unit = (double)slots / (double)units;
             const double eff = 1.0 / (std::max(1.0, per_unit) + 0.1 * per_unit);
-            // larger R amortises shared-memory reads; each extra segment costs a partial round-trip
-            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.0002 * (nseg - 1));
+            // larger R amortises shared-memory reads; an extra segment costs one more FP64 partial per target
+            // (measured: no visible cost up to 64 segments even with 4 source tiles per CTA, N = 2^17 ... 2^20,
+            // profiles/r01_time_modes.txt)
+            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.00003 * (nseg - 1));
             if (score > best_score) {
                 best_score = score;
                 best.variant = (int)(ke - kKernels);
