@@ -912,7 +912,10 @@ static int tree_force(nb_ctx* c) {
         BhTree t = bh_view(c, L);
         StateView s = c->view();
         // resident CTAs only (grid-wide barriers); small worlds do not need the whole device
-        const long long want = blocks_for(std::max<long long>(c->n, 1), kBhBuildThreads);
+        // (developer knob; measured: fewer, fatter CTAs make every level's latency-bound sweep longer — 1024 bodies per
+        //  CTA costs +10-15 % at N = 4096 ... 65536, profiles/r01_bh_sizes.txt)
+        static const long long per_cta = getenv("NB_BH_BODIES_PER_CTA") ? atoll(getenv("NB_BH_BODIES_PER_CTA")) : kBhBuildThreads;
+        const long long want = std::max<long long>(1, (std::max<long long>(c->n, 1) + per_cta - 1) / per_cta);
         const unsigned int grid = (unsigned int)std::min<long long>(want, (long long)c->bh_coop_ctas_per_sm * c->sm_count);
         void* args[] = {&s, &t};
         NB_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bh_build_kernel), dim3(grid), dim3(kBhBuildThreads), args, 0,
