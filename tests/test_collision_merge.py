@@ -128,3 +128,21 @@ def test_device_merge_pass_grid_broad_phase(pkg, oracle_lib, ob, n, spread):
     assert got[0] > 20
     same_outcome(got, oracle_lib.resolve_collisions(pos, vel, mass, pinned, radius, density))
     ph.close()
+
+
+@pytest.mark.gpu
+def test_device_merge_pass_random_small_worlds(pkg, oracle_lib, ob):
+    from test_oracle_random import world
+    rng = np.random.default_rng(4711)
+    ph = pkg.Physics(0)
+    for trial in range(120):
+        n = int(rng.integers(2, 60))
+        pos, vel, mass, pinned = world(rng, n)
+        density = np.full(n, ob.BODY_DENSITY) if rng.random() < 0.5 else rng.uniform(0.5, 6000.0, n)
+        radius = oracle_lib.radius_from_mass(mass, density) * float(rng.choice([0.3, 1.0, 3.0]))
+        ph.upload(pos, vel, mass, pinned)
+        got = ph.resolve_collisions(radius, density, with_log=True)
+        want = oracle_lib.resolve_collisions(pos, vel, mass, pinned, radius, density, with_log=True)
+        same_outcome(got[:8], want[:8])
+        assert np.array_equal(got[8], want[8]), f"trial {trial}: merge order"
+    ph.close()

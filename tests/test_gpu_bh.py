@@ -213,3 +213,27 @@ def test_direct_solver_is_the_default_and_unchanged_by_the_threshold(pkg, oracle
     p.compute_gravity()
     assert np.array_equal(p.download()[2], oracle_lib.compute_gravity(pos, vel, mass))  # 400 <= 512: FP64-exact direct sum
     p.close()
+
+
+def test_random_small_worlds_bitexact(pkg, ph, oracle_lib):
+    """Many small clustered worlds (ties, pins, filtered bodies, theta from 0 to 2.5, epsilon 0): where walk order
+    and float accumulation matter most. Same generator as tests/test_oracle_random.py, which pins the oracle to
+    the live reference on these worlds."""
+    from test_oracle_random import world
+    rng = np.random.default_rng(20261104)
+    done = 0
+    for trial in range(120):
+        n = int(rng.integers(1, 80))
+        pos, vel, mass, pinned = world(rng, n)
+        if len({(np.float32(p[0]), np.float32(p[1])) for p in pos}) < n:
+            continue
+        theta = float(rng.choice([0.0, 0.3, 0.5, 0.5, 1.0, 2.5]))
+        eps = float(rng.choice([0.0, 4.0, 1e6]))
+        ph.set_config(softening=eps)
+        ph.set_solver(pkg.SOLVER_REFERENCE, 0, theta)
+        got = gravity(ph, pos, vel, mass, pinned)
+        want = oracle_lib.bh_gravity(pos, vel, mass, pinned, softening=eps, theta=theta)
+        live = np.isfinite(pos).all(axis=1) & np.isfinite(vel).all(axis=1) & (mass > 0)
+        assert np.array_equal(got[live], want[live]), f"trial {trial}: n={n} theta={theta} eps={eps}"
+        done += 1
+    assert done > 100
