@@ -816,169 +816,7 @@ extern "C" int nb_set_precision(nb_ctx* c, int precision) {
     return NB_OK;
 }
 
-// ---- the reference's Barnes-Hut branch (bh.cuh) ---------------------------------------------------
-namespace {
-
-inline size_t bh_align(size_t v) { return (v + 255) & ~(size_t)255; }
-
-struct BhLayout {
-    size_t bpos, centre, cell, link, count, cur, key, key_out, order_in, order_out, level, ctl, visits, trace, cub, total;
-    size_t cub_bytes;
-};
-
-BhLayout bh_layout(long long rows, long long cells) {
-    BhLayout L{};
-    size_t o = 0;
-    auto take = [&](size_t bytes) { const size_t at = o; o += bh_align(bytes); return at; };
-    L.ctl = take(sizeof(unsigned int) * kBhCtlWords);
-    L.visits = take(sizeof(unsigned long long) * 4);
-    L.level = take(sizeof(int) * (kBhMaxLevels + 2));
-    L.trace = take(sizeof(unsigned long long) * (2 * kBhMaxLevels + 16));
-    L.bpos = take(sizeof(float2) * (size_t)rows);
-    L.cur = take(sizeof(int) * (size_t)rows);
-    L.key = take(sizeof(unsigned int) * (size_t)rows);
-    L.key_out = take(sizeof(unsigned int) * (size_t)rows);
-    L.order_in = take(sizeof(int) * (size_t)rows);
-    L.order_out = take(sizeof(int) * (size_t)rows);
-    L.cub_bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, L.cub_bytes, (unsigned int*)nullptr, (unsigned int*)nullptr, (int*)nullptr,
-                                    (int*)nullptr, (int)rows);
-    L.cub = take(L.cub_bytes);
-    L.centre = take(sizeof(float2) * (size_t)cells);
-    L.cell = take(sizeof(float4) * (size_t)cells);
-    L.link = take(sizeof(int2) * (size_t)cells);
-    L.count = take(sizeof(int) * (size_t)cells);
-    L.total = o;
-    return L;
-}
-
-int ensure_bh(nb_ctx* c, long long cells) {
-    if (!c->h_bh_ctl) NB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_bh_ctl), 256));
-    if (c->bh_scratch && c->bh_rows >= c->n && c->bh_capacity >= cells) return NB_OK;
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    if (c->bh_scratch) cudaFree(c->bh_scratch);
-    c->bh_scratch = nullptr;
-    c->bh_rows = c->bh_capacity = 0;
-    const long long rows = std::max<long long>(c->n, c->bh_rows);
-    const BhLayout L = bh_layout(rows, cells);
-    if (cudaMalloc(&c->bh_scratch, L.total) != cudaSuccess) {
-        cudaGetLastError();
-        return fail(NB_ERR_ALLOC, "Barnes-Hut scratch: out of device memory");
-    }
-    c->bh_bytes = L.total;
-    c->bh_rows = rows;
-    c->bh_capacity = cells;
-    return NB_OK;
-}
-
-BhTree bh_view(const nb_ctx* c, const BhLayout& L) {
-    char* b = static_cast<char*>(c->bh_scratch);
-    BhTree t;
-    t.bpos = reinterpret_cast<float2*>(b + L.bpos);
-    t.centre = reinterpret_cast<float2*>(b + L.centre);
-    t.cell = reinterpret_cast<float4*>(b + L.cell);
-    t.link = reinterpret_cast<int2*>(b + L.link);
-    t.count = reinterpret_cast<int*>(b + L.count);
-    t.cur = reinterpret_cast<int*>(b + L.cur);
-    t.key = reinterpret_cast<unsigned int*>(b + L.key);
-    t.order_in = reinterpret_cast<int*>(b + L.order_in);
-    t.level_begin = reinterpret_cast<int*>(b + L.level);
-    t.ctl = reinterpret_cast<unsigned int*>(b + L.ctl);
-    t.capacity = (int)c->bh_capacity;
-    static const bool trace = getenv("NB_BH_TRACE") != nullptr;  // developer knob: per-phase times on stderr
-    t.trace = trace ? reinterpret_cast<unsigned long long*>(b + L.trace) : nullptr;
-    return t;
-}
-
-}  // namespace
-
-static int exact_force_direct(nb_ctx* c);
-
-// compute_gravity with more than bh_threshold bodies (Physics.hpp:212-230): build, order, walk.
-static int tree_force(nb_ctx* c) {
-    if (c->n > (1ll << 30)) return fail(NB_ERR_INVALID, "Barnes-Hut branch: at most 2^30 bodies");
-    if (c->bh_coop_ctas_per_sm == 0) {
-        int coop = 0;
-        NB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
-        if (!coop) return fail(NB_ERR_CUDA, "device does not support cooperative launches");
-        NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->bh_coop_ctas_per_sm, bh_build_kernel, kBhBuildThreads, 0));
-        if (c->bh_coop_ctas_per_sm < 1) return fail(NB_ERR_CUDA, "bh_build_kernel does not fit on an SM");
-    }
-    long long cells = std::max<long long>(c->bh_capacity, 6 * c->n + 4096);
-    for (int attempt = 0;; ++attempt) {
-        if (cells > (1ll << 30)) return fail(NB_ERR_ALLOC, "Barnes-Hut tree needs more than 2^30 cells");
-        NB_TRY(ensure_bh(c, cells));
-        const BhLayout L = bh_layout(c->bh_rows, c->bh_capacity);
-        BhTree t = bh_view(c, L);
-        StateView s = c->view();
-        // resident CTAs only (grid-wide barriers); small worlds do not need the whole device
-        // (developer knob; measured: fewer, fatter CTAs make every level's latency-bound sweep longer — 1024 bodies per
-        //  CTA costs +10-15 % at N = 4096 ... 65536, profiles/r01_bh_sizes.txt)
-        static const long long per_cta = getenv("NB_BH_BODIES_PER_CTA") ? atoll(getenv("NB_BH_BODIES_PER_CTA")) : kBhBuildThreads;
-        const long long want = std::max<long long>(1, (std::max<long long>(c->n, 1) + per_cta - 1) / per_cta);
-        const unsigned int grid = (unsigned int)std::min<long long>(want, (long long)c->bh_coop_ctas_per_sm * c->sm_count);
-        void* args[] = {&s, &t};
-        NB_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bh_build_kernel), dim3(grid), dim3(kBhBuildThreads), args, 0,
-                                            c->stream));
-        c->kernel_launches++;
-        NB_CUDA(cudaMemcpyAsync(c->h_bh_ctl, t.ctl, sizeof(unsigned int) * kBhCtlWords, cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
-        const unsigned int err = c->h_bh_ctl[kBhError];
-        if (t.trace) {
-            std::vector<unsigned long long> tr(2 * kBhMaxLevels + 16);
-            NB_CUDA(cudaMemcpy(tr.data(), t.trace, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-            fprintf(stderr, "[bh trace] %d stamps, us since start:", (int)tr[0] - 1);
-            for (unsigned long long k = 2; k < tr[0] && k < tr.size(); ++k) fprintf(stderr, " %.1f", (double)(tr[k] - tr[1]) * 1e-3);
-            fprintf(stderr, "\n");
-        }
-        if (err == kBhOverflow) {  // more cells than allocated: the count the build reached is a lower bound
-            cells = std::max<long long>(2 * c->bh_capacity, (long long)c->h_bh_ctl[kBhNodes] + 4096);
-            continue;
-        }
-        if (err == kBhTooDeep)
-            return fail(NB_ERR_INVALID,
-                        "Barnes-Hut branch: two bodies share their float coordinates (the reference's quadtree never "
-                        "separates them, SpatialPartition.hpp:109-156)");
-        c->bh_live = c->h_bh_ctl[kBhLive];
-        if (c->bh_live <= (long long)c->bh_threshold) return exact_force_direct(c);  // :212 counts gathered bodies
-        c->bh_nodes = c->h_bh_ctl[kBhNodes];
-        c->bh_depth = c->h_bh_ctl[kBhDepth];
-        char* b = static_cast<char*>(c->bh_scratch);
-        unsigned int* key_out = reinterpret_cast<unsigned int*>(b + L.key_out);
-        int* order_out = reinterpret_cast<int*>(b + L.order_out);
-        size_t cub_bytes = L.cub_bytes;
-        NB_CUDA(cub::DeviceRadixSort::SortPairs(b + L.cub, cub_bytes, t.key, key_out, t.order_in, order_out, (int)c->n, 0, 32,
-                                                c->stream));
-        unsigned long long* visits = reinterpret_cast<unsigned long long*>(b + L.visits);
-        const unsigned int wgrid = blocks_for(c->n, kBhWalkThreads);
-        if (c->bh_stats) {
-            NB_CUDA(cudaMemsetAsync(visits, 0, sizeof(unsigned long long) * 4, c->stream));
-            bh_walk_kernel<true><<<wgrid, kBhWalkThreads, 0, c->stream>>>(s, t, order_out, c->cfg.g, c->cfg.softening,
-                                                                          c->bh_theta, visits);
-            NB_CUDA(cudaMemcpyAsync(c->h_bh_ctl + 16, visits, sizeof(unsigned long long) * 3, cudaMemcpyDeviceToHost,
-                                    c->stream));
-        } else {
-            bh_walk_kernel<false><<<wgrid, kBhWalkThreads, 0, c->stream>>>(s, t, order_out, c->cfg.g, c->cfg.softening,
-                                                                           c->bh_theta, visits);
-        }
-        NB_CUDA(cudaGetLastError());
-        c->kernel_launches += 3;  // sort (histogram + onesweep passes counted as one library call) + walk
-        c->force_evals++;
-        c->bh_passes++;
-        return NB_OK;
-    }
-}
-
-extern "C" int nb_solver_info(nb_ctx* c, int64_t* values) {
-    if (!c || !values) return fail(NB_ERR_INVALID, "nb_solver_info: null");
-    NB_CUDA(cudaSetDevice(c->device));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    values[0] = c->bh_passes; values[1] = c->bh_nodes; values[2] = c->bh_depth; values[3] = c->bh_live;
-    const unsigned long long* w = reinterpret_cast<const unsigned long long*>(c->h_bh_ctl ? c->h_bh_ctl + 16 : nullptr);
-    for (int k = 0; k < 3; ++k) values[4 + k] = (c->bh_stats && w) ? (int64_t)w[k] : 0;
-    values[7] = 0;
-    return NB_OK;
-}
+#include "host_tree.cuh"  // the reference's Barnes-Hut branch: tree_force(), nb_solver_info
 
 static int exact_force(nb_ctx* c) {
     if (tree_active(c)) return tree_force(c);
@@ -1308,309 +1146,7 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
     return NB_OK;
 }
 
-namespace {
-
-int ensure_collide_scratch(nb_ctx* c, size_t bytes) {
-    if (bytes <= c->collide_bytes) return NB_OK;
-    if (c->collide_scratch) cudaFree(c->collide_scratch);
-    c->collide_scratch = nullptr;
-    c->collide_bytes = 0;
-    NB_CUDA(cudaMalloc(&c->collide_scratch, bytes));
-    c->collide_bytes = bytes;
-    return NB_OK;
-}
-
-inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
-
-// Grid for the broad phase, or cells[0] == 0 when the all-pairs sweep is the better (or only) choice.
-GridSpec plan_grid(int dim, const double lo[3], const double hi[3], double r_max, long long n) {
-    GridSpec g{};
-    g.dim = dim;
-    double ext[3] = {hi[0] - lo[0], hi[1] - lo[1], dim == 3 ? hi[2] - lo[2] : 0.0};
-    const double ext_max = std::max(ext[0], std::max(ext[1], ext[2]));
-    if (!(ext_max > 0.0) || !std::isfinite(ext_max) || !(r_max >= 0.0) || !std::isfinite(r_max)) return g;
-    double h = 2.0 * r_max * (1.0 + 1e-9);
-    h = std::max(h, ext_max * 9.5367431640625e-07);  // at most 2^20 cells per axis
-    const double cap = (double)std::max<long long>(4 * n, 1 << 16);
-    for (int it = 0; it < 8; ++it) {
-        double prod = 1.0;
-        for (int k = 0; k < dim; ++k) prod *= std::floor(ext[k] / h) + 1.0;
-        if (prod <= cap) break;
-        h *= std::pow(prod / cap, 1.0 / dim) * 1.01;
-    }
-    long long prod = 1;
-    for (int k = 0; k < 3; ++k) {
-        g.cells[k] = k < dim ? (int)std::floor(ext[k] / h) + 1 : 1;
-        g.origin[k] = lo[k];
-        prod *= g.cells[k];
-    }
-    g.inv_h = 1.0 / h;
-    // a neighbourhood that covers most of the world is an all-pairs sweep with extra steps
-    if ((double)prod > cap * 1.05 || std::max(g.cells[0], g.cells[1]) < 8) g.cells[0] = 0;
-    return g;
-}
-
-}  // namespace
-
-// Detection over all pairs (all-pairs sweep or grid broad phase). d_pairs (optional, device): sink for the
-// overlapping pairs' keys i * n + j; *n_emitted = how many the kernels tried to append.
-static int overlaps_impl(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair,
-                         unsigned long long* d_pairs, unsigned long long pair_cap, unsigned long long* n_emitted) {
-    NB_CUDA(cudaSetDevice(c->device));
-    const long long n = c->n;
-    const StateView s = c->view();
-    double r_max = 0.0;
-    for (long long i = 0; i < n; ++i) r_max = std::fabs(radius[i]) > r_max || std::isnan(radius[i]) ? std::fabs(radius[i]) : r_max;
-    const char* mode = getenv("NB_OVERLAP_MODE");  // developer/test knob: "pairs" or "grid"
-    const bool want_grid = !(mode && !strcmp(mode, "pairs")) && (n >= 2048 || (mode && !strcmp(mode, "grid")));
-
-    // scratch layout: header (bounds[6], result[2]) | radius | grid arrays
-    const size_t off_radius = 256, off_grid = off_radius + align256(sizeof(double) * (size_t)n);
-    NB_TRY(ensure_collide_scratch(c, off_grid));
-    char* base = static_cast<char*>(c->collide_scratch);
-    unsigned long long* d_bounds = reinterpret_cast<unsigned long long*>(base);
-    unsigned long long* d_res = d_bounds + 6;
-    double* d_radius = reinterpret_cast<double*>(base + off_radius);
-    const unsigned long long init[9] = {~0ull, 0ull, ~0ull, 0ull, ~0ull, 0ull, 0ull, ~0ull, 0ull};
-    NB_CUDA(cudaMemcpyAsync(d_bounds, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(d_radius, radius, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-
-    GridSpec g{};
-    if (want_grid) {
-        const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n, 256), 4 * c->sm_count);
-        collide_bounds_kernel<<<grid, 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, d_bounds);
-        c->kernel_launches++;
-        unsigned long long hb[6];
-        NB_CUDA(cudaMemcpyAsync(hb, d_bounds, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
-        if (hb[0] <= hb[1]) {  // at least one body passed the filter
-            double lo[3], hi[3];
-            for (int k = 0; k < 3; ++k) { lo[k] = dbl_from_order_key(hb[2 * k]); hi[k] = dbl_from_order_key(hb[2 * k + 1]); }
-            g = plan_grid(c->dim, lo, hi, r_max, n);
-        }
-    }
-    if (g.cells[0] > 0) {
-        const size_t n_cells = (size_t)g.cells[0] * g.cells[1] * g.cells[2];
-        size_t cub_bytes = 0;
-        cub::DeviceScan::ExclusiveSum(nullptr, cub_bytes, (unsigned int*)nullptr, (unsigned int*)nullptr, (int)(n_cells + 1), c->stream);
-        const size_t off_count = off_grid, off_start = off_count + align256(4 * (n_cells + 1)),
-                     off_fill = off_start + align256(4 * (n_cells + 1)), off_sorted = off_fill + align256(4 * n_cells),
-                     off_cub = off_sorted + align256(4 * (size_t)n), total = off_cub + align256(cub_bytes);
-        if (total > c->collide_bytes) {  // growing frees the old block: re-stage the header and radii
-            NB_CUDA(cudaStreamSynchronize(c->stream));
-            NB_TRY(ensure_collide_scratch(c, total));
-            base = static_cast<char*>(c->collide_scratch);
-            d_bounds = reinterpret_cast<unsigned long long*>(base);
-            d_res = d_bounds + 6;
-            d_radius = reinterpret_cast<double*>(base + off_radius);
-            NB_CUDA(cudaMemcpyAsync(d_bounds, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
-            NB_CUDA(cudaMemcpyAsync(d_radius, radius, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-        }
-        unsigned int* cell_count = reinterpret_cast<unsigned int*>(base + off_count);
-        unsigned int* cell_start = reinterpret_cast<unsigned int*>(base + off_start);
-        unsigned int* cell_fill = reinterpret_cast<unsigned int*>(base + off_fill);
-        unsigned int* sorted_idx = reinterpret_cast<unsigned int*>(base + off_sorted);
-        NB_CUDA(cudaMemsetAsync(cell_count, 0, 4 * (n_cells + 1), c->stream));
-        NB_CUDA(cudaMemsetAsync(cell_fill, 0, 4 * n_cells, c->stream));
-        grid_bin_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, g, cell_count, nullptr,
-                                                                  nullptr, nullptr);
-        NB_CUDA(cub::DeviceScan::ExclusiveSum(base + off_cub, cub_bytes, cell_count, cell_start, (int)(n_cells + 1), c->stream));
-        grid_bin_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, n, g, nullptr, cell_start,
-                                                                  cell_fill, sorted_idx);
-        grid_overlap_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, g,
-                                                                      cell_start, sorted_idx, d_res, d_pairs, pair_cap);
-        c->kernel_launches += 4;
-        c->overlap_grid_calls++;
-    } else {
-        if (c->dim == 2)
-            overlap_kernel<true><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res, d_pairs, pair_cap);
-        else
-            overlap_kernel<false><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
-                s.x[0], s.x[1], s.x[2], c->mass, d_radius, n, d_res, d_pairs, pair_cap);
-        c->kernel_launches++;
-    }
-    NB_CUDA(cudaGetLastError());
-    unsigned long long res[3];
-    NB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    *n_overlaps = (int64_t)res[0];
-    if (first_pair && res[0]) {
-        first_pair[0] = (int64_t)(res[1] / (unsigned long long)n);
-        first_pair[1] = (int64_t)(res[1] % (unsigned long long)n);
-    }
-    if (n_emitted) *n_emitted = res[2];
-    return NB_OK;
-}
-
-extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair) {
-    if (!c || !n_overlaps) return fail(NB_ERR_INVALID, "nb_count_overlaps: null");
-    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_count_overlaps: single-GPU contexts only (FP64 positions are not replicated)");
-    *n_overlaps = 0;
-    if (first_pair) first_pair[0] = first_pair[1] = -1;
-    if (c->n < 2) return NB_OK;  // Collision.hpp:70
-    if (!radius) return fail(NB_ERR_INVALID, "nb_count_overlaps: null radius array");
-    return overlaps_impl(c, radius, n_overlaps, first_pair, nullptr, 0, nullptr);
-}
-
-// Collision::resolve in its default merge mode (Collision.hpp:49-132). The pair tests run on the device; the
-// merges are replayed on the host in the reference's visiting order as an event queue:
-//   * pairs whose two bodies are untouched so far behave as the initial detection says;
-//   * every merge changes exactly one snapshot (the survivor's): the device re-tests that body against all
-//     living bodies (collide_rescan_kernel) and the hits that still lie AHEAD in the (i, j) order are queued;
-//   * an event is re-tested with the current snapshots when its turn comes.
-// Any pair that overlaps when the reference would test it was detected either initially or by the rescan that
-// followed the last change of one of its bodies, so the replay performs exactly the reference's merges.
-extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const double* density, int64_t* n_merges,
-                                     uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
-                                     uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap) {
-    if (!c || !n_merges || !alive || !changed) return fail(NB_ERR_INVALID, "nb_resolve_collisions: null");
-    if (c->world > 1) return fail(NB_ERR_INVALID, "nb_resolve_collisions: single-GPU contexts only");
-    if (c->dim != 2) return fail(NB_ERR_INVALID, "nb_resolve_collisions: the reference's collision pass is 2-D (nb_upload)");
-    *n_merges = 0;
-    const long long n = c->n;
-    for (long long i = 0; i < n; ++i) { alive[i] = 1; changed[i] = 0; }
-    if (n < 2) return NB_OK;  // Collision.hpp:70
-    if (!radius || !density || !pos_xy || !vel_xy || !mass || !pinned || !radius_out)
-        return fail(NB_ERR_INVALID, "nb_resolve_collisions: null array");
-    NB_CUDA(cudaSetDevice(c->device));
-
-    // scratch of the merge phase: pair sink | cx | cy | hits | live | hit counter
-    unsigned long long pair_cap = (unsigned long long)std::max<long long>(4 * n, 1 << 16);
-    int64_t overlaps = 0;
-    unsigned long long emitted = 0;
-    constexpr long long kMergeFirstHits = 64;  // count + this many hits ride in the first readback
-    size_t off_cx = 0, off_cy = 0, off_hits = 0, off_live = 0, off_cnt = 0;
-    for (;;) {
-        off_cx = align256(sizeof(unsigned long long) * pair_cap);
-        off_cy = off_cx + align256(sizeof(double) * (size_t)n);
-        off_hits = off_cy + align256(sizeof(double) * (size_t)n);
-        off_live = off_hits + align256(sizeof(unsigned int) * ((size_t)n + 1));
-        off_cnt = off_live + align256((size_t)n);
-        const size_t total = off_cnt + 256;
-        if (total > c->merge_bytes) {
-            NB_CUDA(cudaStreamSynchronize(c->stream));
-            if (c->merge_scratch) cudaFree(c->merge_scratch);
-            c->merge_scratch = nullptr;
-            c->merge_bytes = 0;
-            NB_CUDA(cudaMalloc(&c->merge_scratch, total));
-            c->merge_bytes = total;
-        }
-        NB_TRY(overlaps_impl(c, radius, &overlaps, nullptr, static_cast<unsigned long long*>(c->merge_scratch), pair_cap,
-                             &emitted));
-        if (emitted <= pair_cap) break;
-        pair_cap = emitted + 1024;  // more overlapping pairs than the sink held: once more with room for all
-    }
-    if (overlaps == 0) return NB_OK;  // the common frame: resolve() changes nothing
-
-    char* mb = static_cast<char*>(c->merge_scratch);
-    double* d_cx = reinterpret_cast<double*>(mb + off_cx);
-    double* d_cy = reinterpret_cast<double*>(mb + off_cy);
-    unsigned int* d_hits = reinterpret_cast<unsigned int*>(mb + off_hits);  // [0]: running hit total, [1..]: this launch's hits
-    unsigned char* d_live = reinterpret_cast<unsigned char*>(mb + off_live);
-    double* d_cr = reinterpret_cast<double*>(static_cast<char*>(c->collide_scratch) + 256);  // the radii overlaps_impl staged
-
-    // host snapshots (Collision.hpp:51-67): everything the merges read and write
-    std::vector<unsigned long long> keys((size_t)emitted);
-    NB_CUDA(cudaMemcpyAsync(keys.data(), c->merge_scratch, sizeof(unsigned long long) * (size_t)emitted, cudaMemcpyDeviceToHost,
-                            c->stream));
-    const StateView sv = c->view();
-    collide_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], c->mass, n, d_cx, d_cy, d_live);
-    NB_CUDA(cudaMemsetAsync(d_hits, 0, sizeof(unsigned int), c->stream));
-    c->kernel_launches++;
-    if (!c->h_merge) NB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_merge), sizeof(unsigned int) * kMergeFirstHits));
-    std::vector<double> hp(2 * (size_t)n), hv(2 * (size_t)n), hr(radius, radius + n);
-    std::vector<float> hm((size_t)n);
-    std::vector<uint8_t> hpin((size_t)n), hlive((size_t)n);
-    NB_TRY(download_dim(c, hp.data(), hv.data(), nullptr, 2));
-    NB_CUDA(cudaMemcpyAsync(hm.data(), c->mass, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaMemcpyAsync(hpin.data(), c->pinned, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaMemcpyAsync(hlive.data(), d_live, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-
-    std::set<unsigned long long> events(keys.begin(), keys.end());
-    std::vector<unsigned int> hits((size_t)n);
-    const unsigned long long un = (unsigned long long)n;
-    const double pi = 3.141592653589793238462643383279502884;  // std::numbers::pi
-    long long cur_row = -1;
-    bool row_alive = false;
-    int64_t merges = 0;
-    unsigned int hit_base = 0;
-    while (!events.empty()) {
-        const unsigned long long key = *events.begin();
-        events.erase(events.begin());
-        const long long a = (long long)(key / un), b = (long long)(key % un);
-        if (a != cur_row) {  // alive[i] is looked at when row i starts and not again (:76)
-            cur_row = a;
-            row_alive = alive[a] != 0;
-        }
-        if (!row_alive || !alive[b]) continue;  // :76, :78
-        const double dx = hp[2 * b] - hp[2 * a];
-        const double dy = hp[2 * b + 1] - hp[2 * a + 1];
-        const double rsum = hr[a] + hr[b];
-        const double dist2 = dx * dx + dy * dy;
-        if (dist2 > rsum * rsum) continue;  // :85, with the snapshots as they are NOW
-        const bool a_survives = (hm[a] >= hm[b]) || hpin[b];  // :94
-        const long long sv_i = a_survives ? a : b, dd = a_survives ? b : a;
-        if (hpin[dd] && hpin[sv_i]) continue;  // :97-104
-        const double ms = (double)hm[sv_i], md = (double)hm[dd];
-        const double M = ms + md;                                            // :107
-        const double px = ms * hv[2 * sv_i] + md * hv[2 * dd];               // :108-109
-        const double py = ms * hv[2 * sv_i + 1] + md * hv[2 * dd + 1];
-        const double xx = (ms * hp[2 * sv_i] + md * hp[2 * dd]) / M;         // :111-112
-        const double xy = (ms * hp[2 * sv_i + 1] + md * hp[2 * dd + 1]) / M;
-        hm[sv_i] = (float)M;                                                 // :115,128
-        hv[2 * sv_i] = px / M;                                               // :110,116
-        hv[2 * sv_i + 1] = py / M;
-        hp[2 * sv_i] = xx;
-        hp[2 * sv_i + 1] = xy;
-        hpin[sv_i] = (hpin[sv_i] || hpin[dd]) ? 1 : 0;                       // :120,131
-        hr[sv_i] = std::cbrt((3.0 * std::max(1.0, (double)hm[sv_i])) / (4.0 * pi * density[sv_i]));  // :37-46,132
-        changed[sv_i] = 1;
-        const bool newly_dead = alive[dd] != 0;
-        alive[dd] = 0;                                                       // :124-125
-        if (merge_log && merges < merge_log_cap) {
-            merge_log[2 * merges] = sv_i;
-            merge_log[2 * merges + 1] = dd;
-        }
-        ++merges;
-        // which living bodies does the survivor's new state reach? One launch, one readback of the count and
-        // the first hits into pinned memory; the (rare) long hit lists take a second copy.
-        collide_rescan_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, n, sv_i, xx, xy, hr[sv_i],
-                                                                       newly_dead ? dd : -1, d_hits, hit_base);
-        c->kernel_launches++;
-        const size_t first = (size_t)std::min<long long>(kMergeFirstHits, n + 1);
-        NB_CUDA(cudaMemcpyAsync(c->h_merge, d_hits, sizeof(unsigned int) * first, cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
-        const unsigned int n_hits = c->h_merge[0] - hit_base;
-        hit_base = c->h_merge[0];
-        const unsigned int* hit = c->h_merge + 1;
-        if ((size_t)n_hits + 1 > first) {
-            NB_CUDA(cudaMemcpyAsync(hits.data(), d_hits + 1, sizeof(unsigned int) * n_hits, cudaMemcpyDeviceToHost, c->stream));
-            NB_CUDA(cudaStreamSynchronize(c->stream));
-            hit = hits.data();
-        }
-        for (unsigned int h = 0; h < n_hits; ++h) {
-            const unsigned long long k = hit[h];
-            const unsigned long long lo = std::min<unsigned long long>(k, (unsigned long long)sv_i);
-            const unsigned long long hi = std::max<unsigned long long>(k, (unsigned long long)sv_i);
-            const unsigned long long nk = lo * un + hi;
-            if (nk > key) events.insert(nk);  // only tests the reference has not made yet
-        }
-    }
-    NB_CUDA(cudaGetLastError());
-    for (long long i = 0; i < n; ++i) {
-        if (!changed[i]) continue;
-        pos_xy[2 * i] = hp[2 * i]; pos_xy[2 * i + 1] = hp[2 * i + 1];
-        vel_xy[2 * i] = hv[2 * i]; vel_xy[2 * i + 1] = hv[2 * i + 1];
-        mass[i] = hm[i];
-        pinned[i] = hpin[i];
-        radius_out[i] = hr[i];
-    }
-    *n_merges = merges;
-    c->merge_passes++;
-    return NB_OK;
-}
+#include "host_collide.cuh"  // nb_count_overlaps, nb_resolve_collisions
 
 extern "C" int nb_reset_scenario(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_reset_scenario: null context");
