@@ -1,7 +1,7 @@
 """Barnes-Hut branch on the GPU vs the unmodified reference / the oracle: bitwise, plus timings.
-usage: python tools/bh_check.py [n ...]   (run on a GPU box; the reference library is used when present)"""
+usage: python tests/tools/bh_check.py [n ...]   (run on a GPU box; the reference library is used when present)"""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import numpy as np
 import __graft_entry__ as ge

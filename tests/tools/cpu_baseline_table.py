@@ -3,7 +3,7 @@ box's host: force pass alone, diagnostics alone, and the full world.progress() f
 (collision + diagnostics + gravity + integrate), at the sizes BASELINE.md §3 names. One core: the
 reference is single-threaded. Prints a markdown table; a reported baseline, not the target."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT)
 import numpy as np
 import __graft_entry__ as ge
 from oracle import bindings as ob

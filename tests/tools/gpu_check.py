@@ -1,6 +1,6 @@
 """Developer check on a B200: parity numbers and force-kernel variant timings -> stdout."""
 import json, os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import numpy as np
 import __graft_entry__ as ge

@@ -1,7 +1,7 @@
 """Wall time of nb_resolve_collisions (Collision::resolve, merge mode) against the reference / the oracle.
-usage: python tools/time_merge.py   (GPU box)"""
+usage: python tests/tools/time_merge.py   (GPU box)"""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 import numpy as np
 import __graft_entry__ as ge
