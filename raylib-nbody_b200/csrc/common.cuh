@@ -8,9 +8,13 @@
 //   j-stream: FP32 "pair-SoA" packed sources, 32 B per body PAIR:
 //             {x0,x1,y0,y1,z0,z1,m0,m1}; two generations (cur/next) because the fused
 //             epilogue writes step k+1's stream while other CTAs still read step k's.
-//             Positions are scaled by an exact power of two 2^-e (so a float-representable
-//             input is carried unchanged) and masses by 2^-q; G, 2^q and 2^-2e are applied
-//             in FP64 in the epilogue, never rounded to FP32.
+//             Positions are stored RELATIVE TO THE FP64 ORIGIN OF THEIR GROUP of kGroupBodies
+//             consecutive stream rows (GroupHdr), scaled by an exact power of two 2^-e, as a
+//             float `hi` (pk) plus a float residual `lo` (pk_lo): 48 bits of position relative
+//             to the group's extent, whatever the distance of the group from the world origin.
+//             Masses are scaled by 2^-q; G, 2^q and 2^-2e are applied in FP64 in the epilogue.
+//   order   : stream row -> body row. The stream is in Morton (Z) order of the positions so a
+//             group is spatially compact; the FP64 state stays in upload order.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -34,6 +38,22 @@ constexpr int kHeadroomLog2 = 17;         // scaled |x| < 2^17 when packed; r^6 
 constexpr int kMaxSegments = 64;          // j-split factor upper bound
 constexpr float kFarPacked = 1152921504606846976.0f;  // 2^60: packed x of non-attracting rows
 constexpr int kDiagValues = 12;           // KE, PE, Px,Py,Pz, Cx,Cy,Cz, M, nonfinite, pad, pad
+constexpr int kGroupBodies = 128;         // stream rows that share one FP64 origin
+constexpr int kGroupsPerTile = kTileBodies / kGroupBodies;
+// A target closer to a source group's bounding box than kNearFactor x (the box's largest half-extent)
+// takes the two-float (hi + lo) path for that group; everything farther is evaluated from `hi` alone with
+// a relative error of dx below 2^-25 (1 + 2 / kNearFactor).
+constexpr float kNearFactor = 0.5f;
+
+// Origin and half-extents (packed units) of one group of the j-stream. 48 B: three per 16-byte line.
+struct alignas(16) GroupHdr {
+    double c[3];   // FP64 origin, physical units
+    float h[3];    // max |hi| per axis over the group's attracting rows, packed units
+    float reach;   // kNearFactor * max(h)
+    float pad[2];
+};
+static_assert(sizeof(GroupHdr) == 48, "GroupHdr must stay 48 bytes (bulk-copied with the tile)");
+constexpr uint32_t kHdrBytesPerTile = kGroupsPerTile * sizeof(GroupHdr);
 
 // Power-of-two scales for one generation of the j-stream.
 struct Scale {
@@ -79,19 +99,28 @@ enum Mode : int {
     kVerletKick = 1,    // ... + kick of Physics.hpp:309-323
     kVerletKickDrift = 2,  // ... + drift of the NEXT substep (Physics.hpp:297-304) and its pack
     kEuler = 3,         // ... + kick/drift of Physics.hpp:276-290 and the next pack
-    kPartialOnly = 4    // no epilogue: leave the FP64 sums in `part` slot 0 for a later launch
+    kPartialOnly = 4,   // no epilogue: leave the FP64 sums in `part` slot 0 for a later launch
+    kDiagOnly = 5       // potential-only kernels: per-body diagnostics terms, nothing written to the state
 };
 
 struct StepParams {
-    double* x[3];
+    double* x[3];               // positions of generation `gen` (what the force pass evaluates)
+    double* xs[3];              // kVerletKickDrift: the NEXT substep's drifted positions go here (speculative:
+                                // committed by swapping x/xs when the next substep really uses the same dt)
     double* v[3];
     double* a[3];
     double* a0[3];
     const float* mass;
     const uint8_t* pinned;
-    uint8_t* live;              // gather filter of Physics.hpp:198-199, per body
-    const float* pk_cur;        // pair-SoA j-stream being read (generation `gen`)
+    const uint8_t* live;        // gather filter of Physics.hpp:198-199 for generation `gen`, per body row
+    uint8_t* live_next;         // ... for generation gen+1 (written together with the pack)
+    const int* order;           // stream row -> body row, rows [i_lo, i_hi)
+    const float* pk_cur;        // pair-SoA j-stream being read (generation `gen`): hi parts
+    const float* lo_cur;        // pair-SoA residuals {xl0,xl1,yl0,yl1,zl0,zl1,0,0}, read by the near path only
+    const GroupHdr* hdr_cur;    // one per kGroupBodies stream rows
     float* pk_next;             // generation gen+1, written by the epilogue
+    float* lo_next;
+    GroupHdr* hdr_next;
     unsigned int* extent;       // kExtentSlots rotating slots of float bits
     double* part;               // [1 + nseg][4][i_cap] FP64 partial sums: slot 0 carries sums between two
                                 // launches (local / remote sources), slots 1.. the source segments

@@ -208,7 +208,9 @@ force_kernel(const __grid_constant__ StepParams p) {
         float e = 0.f;
         for (int w = 0; w < kWarps; ++w) e = fmaxf(e, red_ext[w]);
         atomicMax(&p.extent[(p.gen + 1) % kExtentSlots], __float_as_uint(e));
-        if (unit == 0) p.extent[(p.gen + 2) % kExtentSlots] = 0u;
+        // recycled by the one CTA that always reaches this epilogue for target tile 0 (with nseg > 1 that is
+        // the last arrival of the tile's segments, whichever segment it carries)
+        if (it == 0) p.extent[(p.gen + 2) % kExtentSlots] = 0u;
     }
     if (POT && tid < 10) {
         double acc = 0.0;
