@@ -4,10 +4,16 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --steps K --warmup W    # the reference's CPU code, same metric
 
-A step = one fused Velocity Verlet step (one force evaluation over N^2 body-body interactions
-+ kick/drift/pack in its epilogue) of config 4: the 2^20-body Plummer sphere, target-partitioned
-over the ranks (one process per GPU, NCCL all-gather of packed positions per step). One JSON
-line on stdout from rank 0; everything else goes to stderr.
+    python bench.py --config 5 --gpus N                      # 2^22-body two-galaxy collision (strong scaling, drift)
+
+A step = one frame of config 4 — the 2^20-body Plummer sphere, Velocity Verlet — issued the way the flecs
+binding issues it: nb_step(ctx, dt, 1). In steady state that is ONE kernel launch per GPU (two when
+sharded: own sources, then remote sources): the force evaluation over N^2 body-body interactions with
+kick, the next frame's drift (into shadow positions, committed by the next call) and its packed stream
+in the epilogue. Targets are partitioned over the ranks (one process per GPU); the all-gather of the
+packed stream is issued behind each step and overlaps the next step's own-sources launch. The line
+carries a parity record against the unmodified reference's full-size accelerations at every rank count
+and exits non-zero when it fails. One JSON line on stdout from rank 0; everything else goes to stderr.
 """
 import argparse
 import json
@@ -123,14 +129,120 @@ def peak_fp32_tflops(sm_count, mhz):
     return sm_count * FP32_LANES_PER_SM * 2 * mhz * 1e6 / 1e12
 
 
+def timed_steps(ph, dt, steps, barrier, reduce_max, diagnostics=False):
+    """K back-to-back steps under ONE CUDA-event pair on the launch stream: no host barrier inside, so a
+    sharded run's exchange overlaps the next step's own-sources launch exactly as in production; each step is
+    preceded by a 256 MiB L2 flush on the same stream (its ~0.05 ms are inside the timed region) and
+    nb_timer_end waits for the last exchange before it records. Returns the max over ranks in ms."""
+    barrier()
+    ph.timer_begin()
+    for _ in range(steps):
+        ph.flush_l2()
+        ph.step(dt, 1, diagnostics=diagnostics)
+    ms = ph.timer_end()
+    barrier()
+    return reduce_max(ms)
+
+
+def fixture_parity(pkg, ph, dist, n):
+    """Reference parity at this rank count, inside the driver-run bench: one compute_gravity over the 2^20-body
+    sphere in the reference's 2-D layout, every rank's rows gathered, against 8192 accelerations the UNMODIFIED
+    reference computed at full size (tests/golden/c4_plummer2d_2e20_subsample.npz, Physics.hpp:231-258).
+    Bound: 1e-5 per body, scaled by the condition number of the sum where a body's pulls cancel (the rule of
+    tests/test_gpu_fullsize.py::test_c4_full_size_against_the_reference_itself)."""
+    path = os.path.join(ROOT, "tests", "golden", "c4_plummer2d_2e20_subsample.npz")
+    if n != (1 << 20) or not os.path.exists(path):
+        return None
+    g = np.load(path)
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=1234, dim=2)
+    eps = float(g["softening"])
+    ph.set_config(softening=eps, integrator=1)
+    ph.upload(pos, vel, mass)
+    ph.compute_gravity()
+    acc = ph.download()[2]
+    if dist is not None:
+        acc = pkg.sharded.gather_rows(dist, acc, n)
+    idx = g["idx"]
+    err = np.linalg.norm(acc[idx] - g["acc"], axis=1) / np.linalg.norm(g["acc"], axis=1)
+    m64 = mass.astype(np.float64)
+    worst, ok = 0.0, True
+    for k in range(len(idx)):
+        e = float(err[k])
+        if e > 5e-6:  # evaluate the conditioning only where it can matter
+            d = pos - pos[idx[k]]
+            r2 = (d * d).sum(axis=1) + eps * eps
+            t = (m64 / (r2 * np.sqrt(r2)))[:, None] * d
+            cond = np.abs(t).sum() / np.linalg.norm(t.sum(axis=0))
+            if cond > 32:
+                ok = ok and (e / cond <= 6e-7)
+                e = e * 32.0 / cond
+        worst = max(worst, e)
+    ok = bool(ok and worst <= 1e-5 and np.isfinite(acc).all())
+    return {"fixture": "tests/golden/c4_plummer2d_2e20_subsample.npz (unmodified reference, full-size pass)",
+            "max_rel_err": worst, "max_rel_err_raw": float(err.max()), "p999": float(np.quantile(err, 0.999)),
+            "median": float(np.median(err)), "n_checked": int(len(idx)), "tolerance": 1e-5,
+            "rule": "per-body |da|/|a| <= 1e-5; bodies with condition number c > 32 are scaled by 32/c", "ok": ok}
+
+
+def state_digest(pkg, ph, dist, n):
+    """Order-independent summary of the state after the timed steps, for comparison across rank counts."""
+    pos, vel, _ = ph.download()
+    if dist is not None:
+        pos, vel = pkg.sharded.gather_rows(dist, pos, n), pkg.sharded.gather_rows(dist, vel, n)
+    t0 = time.perf_counter()
+    d = ph.compute_diagnostics()
+    ph.synchronize()
+    diag_s = time.perf_counter() - t0
+    return {"sum_abs_x": float(np.abs(pos).sum()), "sum_abs_v": float(np.abs(vel).sum()), "energy": d.energy,
+            "kinetic": d.kinetic, "potential": d.potential, "momentum": [float(v) for v in d.momentum],
+            "ok": bool(d.ok),
+            "agreement_expected": "sum_abs_x, sum_abs_v <= 1e-11 relative across rank counts (FP64 state, same "
+                                  "arithmetic, different summation grouping of the sources); energy <= 1e-9"}, diag_s
+
+
+def side_figure(pkg, device, pos, vel, mass, eps, dt, steps, env=None):
+    """The same workload through another kernel variant, timed like the headline: warm-up, then `steps`
+    back-to-back steps with an L2 flush before each, one CUDA-event pair, clocks sampled."""
+    for k, v in (env or {}).items():
+        os.environ[k] = v
+    p = pkg.Physics(device)
+    for k in (env or {}):
+        os.environ.pop(k)
+    p.set_precision(pkg.PRECISION_FP32)
+    p.set_config(softening=eps, integrator=1)
+    p.upload(pos, vel, mass)
+    p.step(dt, 3)
+    p.synchronize()
+    sampler = ClockSampler(device)
+    sampler.start()
+    t0 = time.time()
+    ms = timed_steps(p, dt, steps, p.synchronize, lambda x: x)
+    clocks = sampler.stop(t0, time.time())
+    p.close()
+    n = len(mass)
+    return {"value": float(n) * n * steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": ms / steps,
+            "l2": "flushed before every step", "clocks": clocks}
+
 def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world != args.gpus:
         log(f"note: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE")
-    n = args.n
-    pkg, pos, vel, mass, eps, dt = workload(n, 3)
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    if args.config == 5:
+        n = args.n if args.n_given else (1 << 22)
+        pos, vel, mass = pkg.scenarios.two_galaxies(n, seed=1234, dim=3)
+        eps = 3.844e8 / np.sqrt(n / 2)
+        dt = 1e-3 * pkg.scenarios.crossing_time(n // 2)
+        what = (f"config 5: {n}-body two-galaxy collision (two 3-D Plummer spheres on a bound orbit, equal masses, seed 1234), "
+                f"Velocity Verlet, softening a/sqrt(N/2), dt 1e-3 crossing times, targets partitioned over {world} GPU(s)")
+    else:
+        n = args.n
+        pkg, pos, vel, mass, eps, dt = workload(n, 3)
+        what = (f"config 4: {n}-body Plummer sphere (3-D, equal masses, seed 1234), Velocity Verlet, "
+                f"softening a/sqrt(N), dt 1e-3 crossing times, targets partitioned over {world} GPU(s)")
     dist = None
     if world > 1:
         import torch
@@ -154,36 +266,43 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    warm = max(args.warmup, 3)
     ph.set_precision(pkg.PRECISION_FP32)
     ph.set_config(softening=eps, integrator=1)
     ph.upload(pos, vel, mass)
-    ph.step(dt, 1)  # first frame evaluates a(x0) like the gravity system, then one step
-    for _ in range(max(args.warmup, 3) - 1):
+    ph.step(dt, 1, diagnostics=True)  # first frame evaluates a(x0) like the gravity system, then one step
+    e_first = ph.step_diagnostics().energy
+    for _ in range(warm - 1):
         ph.step(dt, 1)
     barrier()
 
-    # ---- device-resident arm: K steps, L2 flushed between steps, CUDA events on the launch stream
+    # ---- device-resident arm: K back-to-back steps, one CUDA-event pair on the launch stream
     sampler = ClockSampler(local_rank)
     c0 = ph.counters()
     ph.profile_forces(True)
+    ph.overlap_profile(True)
     if rank == 0:
         sampler.start()
     t_wall0 = time.time()
-    total_ms = 0.0
-    for _ in range(args.steps):
-        ph.flush_l2()
-        barrier()
-        ph.timer_begin()
-        ph.step(dt, 1)
-        ms = ph.timer_end()
-        barrier()
-        total_ms += reduce_max(ms)
+    total_ms = timed_steps(ph, dt, args.steps, barrier, reduce_max)
     t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     n_force, force_ms = ph.profile_read()
     ph.profile_forces(False)
+    overlap = ph.overlap_profile(False) if world > 1 else None
     c1 = ph.counters()
     value = float(n) * n * args.steps / (total_ms * 1e-3)
+
+    # ---- what the timed steps left behind: a digest comparable across rank counts, energy drift, and the
+    #      stand-alone diagnostics pass (hot loop B) timed on the same state
+    ph.step(dt, 1, diagnostics=True)
+    e_last = ph.step_diagnostics().energy
+    digest, diag_s = state_digest(pkg, ph, dist, n)
+    digest["steps_taken"] = warm + args.steps + 1
+    digest["rel_energy_drift_fused"] = (e_last - e_first) / abs(e_first)
+    diag_rec = {"seconds": diag_s, "pair_terms_per_s": float(n) * n / diag_s, "n_gpus": world,
+                "note": "nb_compute_diagnostics (Physics.hpp:117-177): extent + pack + potential-only kernel over all "
+                        "N^2 ordered pairs + readback, wall clock with a device synchronise"}
 
     # ---- end-to-end arm: host buffers in, host buffers out, every step (the drop-in's frame)
     lo, hi = ph.local_range()
@@ -202,7 +321,6 @@ def run_ours(args):
         ph.upload_state(h_pos, h_vel, h_acc, h_mass)      # H2D of the frame's inputs
         ph.step(dt, 1)
         ph.download_into(h_pos, h_vel, h_acc)             # D2H of the frame's result rows (synchronises)
-        barrier()
         if k > 0:  # first one warms the staging buffers
             e2e_ms += reduce_max((time.perf_counter() - t0) * 1e3)
         if dist is not None:  # untimed host plumbing: every rank re-uploads the full state next frame
@@ -212,43 +330,49 @@ def run_ours(args):
     h2d = (hi - lo) * (3 * 3 * 8 + 4 + 0)   # nb_upload_state copies a rank's own rows only (the rest arrive as FP32 sources over NVLink)
     d2h = (hi - lo) * 3 * 3 * 8
 
-    general = None
-    planar = None
-    if world == 1:
+    general = planar = config3 = None
+    if world == 1 and args.config == 4 and args.sides:
         # the same workload through the general-mass kernel (the production run above uses the
         # uniform-mass variant because every body of config 4 has the same mass)
-        os.environ["NB_FORCE_GENERIC"] = "1"
-        pg = pkg.Physics(local_rank)
-        os.environ.pop("NB_FORCE_GENERIC")
-        pg.set_precision(pkg.PRECISION_FP32)
-        pg.set_config(softening=eps, integrator=1)
-        pg.upload(pos, vel, mass)
-        pg.step(dt, 2)
-        pg.synchronize()
-        pg.timer_begin()
-        pg.step(dt, 2)
-        g_ms = pg.timer_end()
-        pg.close()
-        general = {"value": float(n) * n * 2 / (g_ms * 1e-3), "unit": UNIT, "steps": 2,
-                   "note": "NB_FORCE_GENERIC=1: per-source masses multiplied in the kernel (12 instead of 11 FMA-pipe ops per pair)"}
+        general = side_figure(pkg, local_rank, pos, vel, mass, eps, dt, max(args.steps, 5), env={"NB_FORCE_GENERIC": "1"})
+        general["note"] = "NB_FORCE_GENERIC=1: per-source masses multiplied in the kernel (12 instead of 11 FMA-pipe ops per pair)"
         # and the reference's own layout: the same sphere projected to z = 0 and uploaded as 2-D
         # (Position/Velocity are DVec2), which selects the planar kernel variant
         p2, v2, m2 = pkg.scenarios.plummer(n, seed=1234, dim=2)
-        pp = pkg.Physics(local_rank)
-        pp.set_precision(pkg.PRECISION_FP32)
-        pp.set_config(softening=eps, integrator=1)
-        pp.upload(p2, v2, m2)
-        pp.step(dt, 2)
-        pp.synchronize()
-        pp.timer_begin()
-        pp.step(dt, 2)
-        p_ms = pp.timer_end()
-        pp.close()
-        planar = {"value": float(n) * n * 2 / (p_ms * 1e-3), "unit": UNIT, "steps": 2,
-                  "note": "2-D reference layout (z = 0): 8 FMA-pipe ops per pair; counted as interactions, not as 20-FLOP work"}
+        planar = side_figure(pkg, local_rank, p2, v2, m2, eps, dt, max(args.steps, 5))
+        planar["note"] = "2-D reference layout (z = 0): 8 FMA-pipe ops per pair; counted as interactions, not as 20-FLOP work"
+        # config 3: 65536-body Plummer sphere, Verlet, fused energy/momentum diagnostics read back every step
+        n3 = 65536
+        p3, v3, m3 = pkg.scenarios.plummer(n3, seed=1234, dim=3)
+        eps3, dt3 = 3.844e8 / np.sqrt(n3), 1e-3 * pkg.scenarios.crossing_time(n3)
+        q = pkg.Physics(local_rank)
+        q.set_precision(pkg.PRECISION_FP32)
+        q.set_config(softening=eps3, integrator=1)
+        q.upload(p3, v3, m3)
+        q.step(dt3, 5)
+        q.synchronize()
+        k3 = 50
+        q.timer_begin()
+        q.step(dt3, k3)
+        plain_ms = q.timer_end() / k3
+        t0 = time.perf_counter()
+        for _ in range(k3):
+            q.step(dt3, 1, diagnostics=True)
+            d3 = q.step_diagnostics()      # blocking read-back of the 12 sums
+        diag_ms = (time.perf_counter() - t0) * 1e3 / k3
+        q.timer_begin()
+        for _ in range(10):
+            q.compute_diagnostics()
+        alone_ms = q.timer_end() / 10
+        q.close()
+        config3 = {"n_bodies": n3, "plain_step_ms": plain_ms, "step_with_diagnostics_readback_ms": diag_ms,
+                   "interactions_per_s_plain": float(n3) * n3 / (plain_ms * 1e-3),
+                   "interactions_per_s_with_diagnostics": float(n3) * n3 / (diag_ms * 1e-3),
+                   "standalone_diagnostics_ms": alone_ms, "energy": d3.energy,
+                   "note": "config 3: per-step energy/momentum diagnostics from the fused potential (wall clock incl. read-back)"}
 
     tree = None
-    if world == 1 and args.tree:
+    if world == 1 and args.tree and args.config == 4:
         # The reference's DEFAULT solver at this body count: above bh_threshold = 100 bodies its
         # compute_gravity is a float Barnes-Hut quadtree (Physics.hpp:212-230), reproduced bit for bit
         # by NB_SOLVER_REFERENCE. Not the headline metric (a tree pass does ~600 cell visits per
@@ -291,6 +415,18 @@ def run_ours(args):
                 tree["cpu_seconds_per_pass"] = time.perf_counter() - t0
                 tree["cpu_kind"] = "port"
 
+    # ---- reference parity at THIS rank count (every rank takes part; rank 0 reports)
+    near = None
+    parity = None
+    if args.config == 4 and args.parity:
+        ph.near_stats(True)
+        parity = fixture_parity(pkg, ph, dist, n)
+        visits, near_visits = ph.near_stats(False)
+        near = {"warp_group_visits": visits, "near_path_visits": near_visits,
+                "near_fraction": near_visits / max(visits, 1),
+                "note": "share of (warp, 128-row source group) visits that took the two-float path in the parity pass"}
+
+    status = 0
     if rank == 0:
         props_sms = ph.device_info()["sm_count"]
         peaks = {}
@@ -301,7 +437,7 @@ def run_ours(args):
         max_mhz = float(peaks.get("sm_max_mhz", 1965.0))
         peak = peak_fp32_tflops(props_sms, max_mhz)
         per_gpu_inter = float(n) * (hi - lo)   # rank 0's share of one force evaluation
-        kern_s = force_ms * 1e-3 / max(n_force, 1) * (n_force / max(args.steps, 1))  # force time per step
+        kern_s = force_ms * 1e-3 / max(args.steps, 1)  # force-kernel time per step (own + remote launches)
         achieved = per_gpu_inter * FLOPS_PER_INTERACTION / kern_s / 1e12
         traffic = None
         try:
@@ -320,29 +456,41 @@ def run_ours(args):
         cpu = cpu_baseline(n_cpu, eps) if n_cpu > 0 else None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32 pair terms / f64 accumulation+state",
             "data": "synthetic",
-            "config": {"workload": f"config 4: {n}-body Plummer sphere (3-D, equal masses, seed 1234), Velocity Verlet, "
-                                   f"softening a/sqrt(N), dt 1e-3 crossing times, targets partitioned over {world} GPU(s)",
-                       "n_bodies": n, "interactions_per_step": float(n) * n, "integrator": "velocity_verlet",
-                       "l2": "flushed (256 MiB memset) before every timed step", "parallelism": f"target-partition x{world}"},
+            "config": {"workload": what, "n_bodies": n, "interactions_per_step": float(n) * n,
+                       "integrator": "velocity_verlet",
+                       "l2": "flushed (256 MiB memset on the launch stream) before every timed step",
+                       "timing": "one CUDA-event pair around the K back-to-back steps (flushes included, no host barrier "
+                                 "inside; the pair closes after the last step's exchange), max over ranks",
+                       "parallelism": f"target-partition x{world}"},
             "pct_fp32_peak": 100.0 * value * FLOPS_PER_INTERACTION / (peak * 1e12 * world),
             "steps_per_s": 1e3 * args.steps / total_ms,
-            "kernel_variant": "uniform-mass (all bodies of config 4 have equal mass)", "general_mass": general, "planar_2d": planar,
-            "reference_solver": tree,
+            "kernel_variant": "uniform-mass (all bodies of this workload have equal mass)", "general_mass": general,
+            "planar_2d": planar, "config3": config3, "reference_solver": tree, "diagnostics": diag_rec,
             "roofline": roof, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
                     "path": "nb_upload_state (pinned host) -> nb_step -> nb_download3 (pinned host), wall clock"},
             "gpu_launches": c1["kernel_launches"] - c0["kernel_launches"],
+            "launches_note": "kernels of this library inside the timed region, per rank: one fused force launch per step at "
+                             "1 GPU, two (own / remote sources) when sharded; the L2-flush memsets are not kernels of the library",
+            "parity": parity, "near_path": near, "state_digest": digest, "exchange_overlap": overlap,
             "clocks": clocks,
         }
         emit(line)
+        if parity is not None and not parity["ok"]:
+            log(f"PARITY FAILED at {world} GPU(s): {parity}")
+            status = 3
+        if not digest["ok"]:
+            log("diagnostics of the end state are not finite")
+            status = 3
     ph.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    return status
 
 
 def run_reference(args):
@@ -389,7 +537,11 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=1 << 20, help="bodies (BASELINE metric: 2^20)")
+    ap.add_argument("--n", type=int, default=None, help="bodies (BASELINE metric: 2^20; config 5: 2^22)")
+    ap.add_argument("--config", type=int, default=4, choices=[4, 5], help="BASELINE.json configs[3] (default) or configs[4]")
+    ap.add_argument("--no-parity", dest="parity", action="store_false", help="skip the fixture parity pass")
+    ap.add_argument("--no-sides", dest="sides", action="store_false",
+                    help="skip the general-mass / planar / config-3 side figures")
     ap.add_argument("--no-tree", dest="tree", action="store_false",
                     help="skip the extra figure for the reference's default Barnes-Hut solver")
     # sample sizes are deliberately not powers of two: the reference's loop streams pos[j] and acc[j]
@@ -398,11 +550,14 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=30000, help="bodies in the cpu_baseline sample (0 = skip)")
     ap.add_argument("--ref-sample", type=int, default=20000, help="bodies per step of --impl reference")
     args = ap.parse_args()
+    args.n_given = args.n is not None
+    if args.n is None:
+        args.n = 1 << 20
     if args.impl == "reference":
         run_reference(args)
-    else:
-        run_ours(args)
+        return 0
+    return run_ours(args)
 
 
 if __name__ == "__main__":
-    main()
+    sys.exit(main())

@@ -252,6 +252,15 @@ int nb_counters(nb_ctx* ctx, int64_t* kernel_launches, int64_t* force_evals, dou
  * launch when profiling is on). */
 int nb_profile_forces(nb_ctx* ctx, int enable);
 int nb_profile_read(nb_ctx* ctx, int64_t* n_launches, double* total_ms);
+/* Sharded contexts, Velocity Verlet: CUDA events around the last own-sources launch and around the exchange
+ * (all-gather of the packed stream) it overlapped. ms4 = {own-sources launch duration, exchange start and
+ * exchange end relative to the launch's start (negative = before it), exchange duration}. Call after a step;
+ * enable = 1 arms the events for the following steps. Synchronises. */
+int nb_overlap_profile(nb_ctx* ctx, int enable, float* ms4);
+/* Developer counters of the force kernel's two-float ("near") path: how many (warp, source group) visits
+ * the launches since the last call made and how many of them took the near path. Reads and clears the
+ * counters; enable = 0 also releases them (the kernel then skips the counting). Synchronises. */
+int nb_near_stats(nb_ctx* ctx, int enable, int64_t* visits, int64_t* near_visits);
 
 #ifdef __cplusplus
 }

@@ -13,7 +13,7 @@
 //             float `hi` (pk) plus a float residual `lo` (pk_lo): 48 bits of position relative
 //             to the group's extent, whatever the distance of the group from the world origin.
 //             Masses are scaled by 2^-q; G, 2^q and 2^-2e are applied in FP64 in the epilogue.
-//   order   : stream row -> body row. The stream is in Morton (Z) order of the positions so a
+//   order   : stream row -> body row. The stream is in Hilbert-curve order of the positions so a
 //             group is spatially compact; the FP64 state stays in upload order.
 #pragma once
 #include <cuda_runtime.h>
@@ -43,13 +43,16 @@ constexpr int kGroupsPerTile = kTileBodies / kGroupBodies;
 // A target closer to a source group's bounding box than kNearFactor x (the box's largest half-extent)
 // takes the two-float (hi + lo) path for that group; everything farther is evaluated from `hi` alone with
 // a relative error of dx below 2^-25 (1 + 2 / kNearFactor).
-constexpr float kNearFactor = 0.5f;
+#ifndef NB_NEAR_FACTOR
+#define NB_NEAR_FACTOR 0.25f
+#endif
+constexpr float kNearFactor = NB_NEAR_FACTOR;
 
 // Origin and half-extents (packed units) of one group of the j-stream. 48 B: three per 16-byte line.
 struct alignas(16) GroupHdr {
-    double c[3];   // FP64 origin, physical units
     float h[3];    // max |hi| per axis over the group's attracting rows, packed units
     float reach;   // kNearFactor * max(h)
+    double c[3];   // FP64 origin in packed units (physical origin * 2^-e, exact)
     float pad[2];
 };
 static_assert(sizeof(GroupHdr) == 48, "GroupHdr must stay 48 bytes (bulk-copied with the tile)");
@@ -126,6 +129,7 @@ struct StepParams {
                                 // launches (local / remote sources), slots 1.. the source segments
     unsigned int* tile_counter; // [n_itiles] arrival counters (only nseg > 1)
     double* diag_part;          // [n_itiles][kDiagValues] per-CTA diagnostics partials
+    unsigned long long* stats;  // null, or {warp x group visits, near ones} (nb_near_stats)
     long long n;                // bodies
     long long n_tiles;          // j-stream length in tiles of kTileBodies (padded with m = 0)
     long long i_lo, i_hi;       // target range owned by this rank
@@ -133,8 +137,10 @@ struct StepParams {
     long long j_tile_lo, j_tile_hi;  // LOGICAL source tiles this launch covers, split over nseg CTAs
     long long hole_lo, hole_len;     // logical tile t >= hole_lo maps to physical tile t + hole_len
                                      // (the remote-sources launch skips the rank's own tiles this way)
+    long long row_cap;          // end of this rank's padded stream rows (groups at or beyond it are never packed)
     int nseg;
     int gen;
+    int slot_cur, slot_nxt;     // extent slots: scale of the stream being read / of the one the epilogue packs
     int mode;
     int accumulate;             // 1: add `part` slot 0 (an earlier launch's sums) before the epilogue
     int mass_exp;

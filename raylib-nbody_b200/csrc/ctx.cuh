@@ -51,11 +51,24 @@ struct nb_ctx {
     long long lo = 0, hi = 0; // rows owned by this rank
     long long n_tiles = 0;    // j-stream tiles (padded to world * tiles_per_rank)
     long long tiles_per_rank = 0;
-    double* state = nullptr;  // 12 * cap doubles: x[3], v[3], a[3], a0[3]
+    double* state = nullptr;  // 15 * cap doubles: x[3], v[3], a[3], a0[3], and the shadow positions xs[3]
+    int x_sel = 0;            // which of the two position slots (0: rows 0-2, 1: rows 12-14) is Position
     float* mass = nullptr;
     uint8_t* pinned = nullptr;
-    uint8_t* live = nullptr;
-    float* pk[2] = {nullptr, nullptr};  // pair-SoA j-stream generations
+    uint8_t* live2[2] = {nullptr, nullptr};  // gather-filter flags per generation parity (body rows)
+    int* order = nullptr;               // stream row -> body row (Hilbert-curve order of this rank's rows)
+    float* pk[2] = {nullptr, nullptr};  // pair-SoA j-stream generations: hi parts
+    float* pk_lo[2] = {nullptr, nullptr};   // ... residuals (near path)
+    nb::GroupHdr* hdr[2] = {nullptr, nullptr};  // ... group origins / half-extents
+    float* dpk = nullptr;               // stand-alone diagnostics stream (hi, lo, headers)
+    float* dpk_lo = nullptr;
+    nb::GroupHdr* dhdr = nullptr;
+    unsigned long long* sort_keys[2] = {nullptr, nullptr};
+    int* sort_vals[2] = {nullptr, nullptr};
+    void* sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    bool order_valid = false;           // `order` was sorted for this upload
+    long long packs_since_sort = 0;     // generations packed since the last sort (re-sorted every kResortEvery)
     unsigned int* extent = nullptr;     // kExtentSlots + 4 slots
     double* part = nullptr;             // FP64 partial sums, (1 + part_slots) * 4 * i_cap
     long long i_cap = 0;
@@ -66,7 +79,6 @@ struct nb_ctx {
     long long diag_part_rows = 0;
     double* totals = nullptr;           // device scratch for fixed-order final sums (64 doubles)
     double* h_totals = nullptr;         // pinned host mirror
-    float4* dpk = nullptr;              // stand-alone diagnostics pack
     void* l2_scratch = nullptr;         // 256 MiB, nb_flush_l2
     void* staging = nullptr;            // device staging for AoS uploads/downloads
     void* collide_scratch = nullptr;    // nb_count_overlaps: radii, grid arrays, scan temp
@@ -95,21 +107,34 @@ struct nb_ctx {
     int gen = 0;               // generation of pk[gen & 1]
     int mass_exp = 0;          // masses are packed as m * 2^-mass_exp
     bool uniform_mass = false; // every body that can attract has the same mass -> no m*w multiply in the kernel
+    bool diag_uniform_mass = false;  // EVERY body has that mass (compute_diagnostics counts all of them)
     double uniform_packed_mass = 1.0;
     bool planar = false;       // 2-D upload: z == 0 forever -> kernels skip the z terms
     bool force_generic = false;
     bool acc_valid = false;    // Acceleration == a(x) for the current positions
     bool packed_valid = false; // pk[gen & 1] matches the current positions
+    // Velocity Verlet: every kick epilogue also drifts the NEXT substep into the shadow positions and packs
+    // generation gen+1 from them. The next substep commits that (swap x/xs, gen += 1) when it uses the same
+    // dt and nothing touched the state in between; otherwise it is discarded.
+    bool spec_valid = false;
+    double spec_h = 0.0;
+    int spec_kind = 0;         // kernel kind (0 force, 1 force + potential) of the pass that prepared it
     bool step_diag_valid = false;
     long long step_diag_rows = 0;
 
     // ---- launch plans ----
-    nb::LaunchPlan plans[3][2];  // [all | own sources | remote sources][without / with potential]
-    int forced_r = 0, forced_packed = -1, forced_nseg = 0, forced_chunk = nb::kFlushChunk, forced_minb = 4;
+    nb::LaunchPlan plans[3][3];  // [all | own sources | remote sources][force | force + potential | potential only]
+    int forced_r = 0, forced_nseg = 0;
+    int resort_every = 64;     // generations between two Hilbert sorts of the stream (NB_RESORT_EVERY)
 
     // ---- measurement ----
     long long kernel_launches = 0;
     long long force_evals = 0;
+    long long sorts = 0;
+    unsigned long long* near_stats = nullptr;  // device counters of nb_near_stats
+    bool profile_comm = false;           // record ev_comm0/1 around every exchange (overlap evidence)
+    cudaEvent_t ev_comm0[2] = {nullptr, nullptr}, ev_comm1[2] = {nullptr, nullptr};  // per generation parity
+    cudaEvent_t ev_own0 = nullptr, ev_own1 = nullptr;
     double interactions = 0.0;
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // pairs
@@ -119,17 +144,20 @@ struct nb_ctx {
     void* nccl_comm = nullptr;
 
     double* sx(int c) const { return state + (long long)c * cap; }
+    double* pos_slot(int sel, int k) const { return sx((sel ? 12 : 0) + k); }
+    uint8_t* live() const { return live2[gen & 1]; }
+    void drop_speculation() { spec_valid = false; }
     nb::StateView view() const {
         nb::StateView s;
         for (int k = 0; k < 3; ++k) {
-            s.x[k] = sx(k);
+            s.x[k] = pos_slot(x_sel, k);
             s.v[k] = sx(3 + k);
             s.a[k] = sx(6 + k);
             s.a0[k] = sx(9 + k);
         }
         s.mass = mass;
         s.pinned = pinned;
-        s.live = live;
+        s.live = live();
         s.n = n;
         s.lo = lo;
         s.hi = hi;

@@ -1,9 +1,13 @@
 // diag.cuh — stand-alone Physics::compute_diagnostics (src/systems/Physics.hpp:117-177):
 // KE, PE, E, P, COM, M over ALL bodies, unfiltered (unlike the gravity gather filter).
 // PE = -G sum_{i<j} m_i m_j / sqrt(r^2+eps^2) is evaluated as -G/2 sum_i m_i phi_i with
-// phi_i = sum_{j != i} m_j / r_ij in FP32 per 32-source chunk, FP64 across chunks; every
-// other sum is FP64. Warp-shuffle + block reduction per CTA, then a fixed-order final pass
-// (sum_rows_kernel), so results are bit-reproducible.
+// phi_i = sum_{j != i} m_j / r_ij by the potential-only instantiation of the force kernel
+// (force_kernel<..., PONLY>: TMA ring, pair records, R targets per thread, 7 FMA-pipe instructions
+// per source pair) over a stream packed with this function's own rules (pack_kernel<true>: every body
+// with a finite position, raw masses); every other sum is FP64 in that kernel's epilogue
+// (diag_accumulate). Warp-shuffle + block reduction per CTA, then a fixed-order final pass
+// (sum_rows_kernel), so results are bit-reproducible. This file keeps the extent pass and the FP64
+// kernel of the exact path.
 #pragma once
 #include "epilogue.cuh"
 #include "ptx.cuh"
@@ -31,84 +35,6 @@ __global__ void __launch_bounds__(kDiagThreads) diag_extent_kernel(const double*
     if (threadIdx.x == 0) {
         for (int w = 1; w < kDiagThreads / 32; ++w) e = fmaxf(e, red[w]);
         atomicMax(&extent[kDiagExtentSlot], __float_as_uint(e));
-    }
-}
-
-// AoS float4 {x,y,z,m} in packed units for every body (raw mass, any sign), rows [lo,hi).
-__global__ void __launch_bounds__(kDiagThreads) diag_pack_kernel(const double* x0, const double* x1,
-                                                                 const double* x2, const float* mass, long long lo,
-                                                                 long long hi, const unsigned int* extent,
-                                                                 int mass_exp, float4* out) {
-    const long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= hi) return;
-    const Scale sc = scale_for(extent[kDiagExtentSlot], mass_exp, 1.0, 0.f);
-    const double x[3] = {x0[i], x1[i], x2[i]};
-    const bool fin = finite_d(x[0]) && finite_d(x[1]) && finite_d(x[2]);
-    float4 r;
-    r.x = fin ? (float)(x[0] * sc.inv_len) : 0.f;
-    r.y = fin ? (float)(x[1] * sc.inv_len) : 0.f;
-    r.z = fin ? (float)(x[2] * sc.inv_len) : 0.f;
-    r.w = fin ? (float)((double)mass[i] * pow2d(-mass_exp)) : 0.f;
-    out[i] = r;
-}
-
-// One target per thread over all n sources; per-CTA partial diagnostics -> part[blockIdx][kDiagValues].
-__global__ void __launch_bounds__(kDiagThreads) diag_potential_kernel(
-    const float4* __restrict__ dpk, long long n, long long lo, long long hi, const double* x0, const double* x1,
-    const double* x2, const double* v0, const double* v1, const double* v2, const float* mass,
-    const unsigned int* extent, int mass_exp, double g, float softening, double* part) {
-    __shared__ float4 tile[kDiagThreads];
-    __shared__ double red[kDiagThreads / 32][kDiagValues];
-    const Scale sc = scale_for(extent[kDiagExtentSlot], mass_exp, g, 0.f);
-    const double epsd = (double)softening * sc.inv_len;
-    const float eps2 = (float)(epsd * epsd);  // no floor: eps = 0 stays 0 as in the reference
-    const long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    const bool valid = i < hi;
-    const float4 me = dpk[valid ? i : lo];
-    double phi = 0.0;
-    for (long long j0 = 0; j0 < n; j0 += kDiagThreads) {
-        const long long j = j0 + threadIdx.x;
-        tile[threadIdx.x] = j < n ? dpk[j] : make_float4(0.f, 0.f, 0.f, 0.f);
-        __syncthreads();
-#pragma unroll 1
-        for (int c = 0; c < kDiagThreads; c += 32) {
-            float ph = 0.f;
-#pragma unroll
-            for (int u = 0; u < 32; ++u) {
-                const float4 b = tile[c + u];
-                const float dx = b.x - me.x, dy = b.y - me.y, dz = b.z - me.z;
-                float r2 = __fmaf_rn(dx, dx, eps2);
-                r2 = __fmaf_rn(dy, dy, r2);
-                r2 = __fmaf_rn(dz, dz, r2);
-                // i < j pairs only: no self term. r2 == 0 between distinct bodies (eps = 0,
-                // coincident) gives inf like the reference's 1/sqrt(0) and trips `ok`.
-                const float rs = (j0 + c + u == i) ? 0.f : rsqrt_fast(r2);
-                ph = __fmaf_rn(b.w, rs, ph);
-            }
-            phi += (double)ph;
-        }
-        __syncthreads();
-    }
-    DiagTerms dg;
-#pragma unroll
-    for (int k = 0; k < kDiagValues; ++k) dg.v[k] = 0.0;
-    if (valid) {
-        const double x[3] = {x0[i], x1[i], x2[i]};
-        const double v[3] = {v0[i], v1[i], v2[i]};
-        diag_accumulate(dg, x, v, mass[i], phi * sc.pot_unit, g, true);
-    }
-#pragma unroll
-    for (int k = 0; k < 10; ++k) {
-        double w = dg.v[k];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = w;
-    }
-    __syncthreads();
-    if (threadIdx.x < 10) {
-        double w = 0.0;
-        for (int q = 0; q < kDiagThreads / 32; ++q) w += red[q][threadIdx.x];
-        part[(long long)blockIdx.x * kDiagValues + threadIdx.x] = w;
     }
 }
 

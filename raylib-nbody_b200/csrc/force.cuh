@@ -139,26 +139,34 @@ __device__ __forceinline__ void self_mask(f2 mj, long long j0, long long row, f2
 }
 
 // One flush chunk (CH sources = CH/2 pair records) against R targets, hi parts only.
-// MASK: the chunk may contain one of this CTA's own targets (stream rows row0 + r*NT); its mass is
+// MASK: the chunk may contain one of this thread's own targets (stream rows row0 + r*RS); its mass is
 // zeroed for that target so the potential carries no self term (the force self term is exactly 0 anyway).
-template <int R, bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY, int NT>
+template <int R, bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY, int RS>
 __device__ __forceinline__ void chunk_interact(Target<POT, EQM, D2, PONLY> (&t)[R], const float4* __restrict__ rec,
                                                float eps2, long long j_first, long long row0) {
     const f2 e2 = f2_make(eps2, eps2);
     const f2 zero = f2_make(0.f, 0.f);
-#pragma unroll kUnrollPairs
-    for (int u = 0; u < CH / 2; ++u) {
-        f2 xj, yj, zj, mj;
-        load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);
+    if constexpr (MASK) {
+        // the one tile of a launch that holds the CTA's own targets: kept rolled (the per-pair self masks
+        // of a fully unrolled body cost more registers than the whole hot loop)
+#pragma unroll 2
+        for (int u = 0; u < CH / 2; ++u) {
+            f2 xj, yj, zj, mj;
+            load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            if (MASK) {
+            for (int r = 0; r < R; ++r) {
                 f2 m, bump;
-                self_mask<EQM>(mj, j_first + 2 * u, row0 + (long long)r * NT, m, bump);
+                self_mask<EQM>(mj, j_first + 2 * u, row0 + (long long)r * RS, m, bump);
                 t[r].template interact<true>(xj, yj, zj, m, e2, bump);
-            } else {
-                t[r].template interact<false>(xj, yj, zj, mj, e2, zero);
             }
+        }
+    } else {
+#pragma unroll kUnrollPairs
+        for (int u = 0; u < CH / 2; ++u) {
+            f2 xj, yj, zj, mj;
+            load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);
+#pragma unroll
+            for (int r = 0; r < R; ++r) t[r].template interact<false>(xj, yj, zj, mj, e2, zero);
         }
     }
 }

@@ -1,16 +1,23 @@
 // force_kernel.cuh — grid/CTA structure of the force kernel (see force.cuh for the math).
 //
 // Grid: one CTA per (target tile, source segment). A target tile is NT*R consecutive
-// bodies (thread t owns bodies i0 + r*NT + t, so all FP64 state traffic is coalesced);
-// the source range of the launch is split into `nseg` tile-aligned segments so the grid
-// can be sized to a whole number of waves of 148 SMs for any N. With nseg > 1 each CTA
-// leaves FP64 partial sums in `part`; the last CTA to arrive for a target tile adds them
-// in fixed segment order (bit-reproducible regardless of arrival order) and runs the epilogue.
+// STREAM rows; warp w owns the 32*R consecutive rows row0 + w*32*R + r*32 + lane, so in Hilbert order
+// a warp's targets are one compact clump and few source groups are "near" it (`order` maps a stream
+// row to its body row in the FP64 state, which stays in upload order); the source range of the launch is split into
+// `nseg` tile-aligned segments so the grid can be sized to a whole number of waves of 148 SMs for
+// any N. With nseg > 1 each CTA leaves FP64 partial sums in `part`; the last CTA to arrive for
+// a target tile adds them in fixed segment order (bit-reproducible regardless of arrival order)
+// and runs the epilogue.
 //
 // The j-stream reaches shared memory through a kStages-deep ring of 1-D TMA bulk copies
-// (cp.async.bulk + mbarrier complete_tx): one elected thread issues 8 KB copies, nobody
-// spends issue slots on loads, and every warp reads sources with broadcast LDS.128. Stages are
-// handed back through `empty` mbarriers (one arrival per warp), not a CTA-wide barrier.
+// (cp.async.bulk + mbarrier complete_tx): one elected thread issues an 8 KB copy of the tile's
+// pair records plus a 192 B copy of its four group headers, nobody spends issue slots on loads,
+// and every warp reads sources with broadcast LDS.128. A stage is handed back with a CTA-wide
+// barrier per tile (NB_RING_SYNC 1, the shipped setting; per-warp `empty` mbarriers measured 4 % slower).
+//
+// Per source group (128 rows) every thread re-bases its R targets on the group's FP64 origin
+// (positions of the CTA's targets sit in shared memory as FP64) and decides, warp-uniformly, between
+// the one-float path and the two-float near path (force.cuh).
 #pragma once
 #include "epilogue.cuh"
 #include "force.cuh"
@@ -23,43 +30,59 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <int NT, int R, bool PACKED, bool POT, int MINB, int CH = kFlushChunk, bool EQM = false, bool D2 = false>
+template <int NT, int R, bool POT, int MINB, int CH = kFlushChunk, bool EQM = false, bool D2 = false,
+          bool PONLY = false>
 __global__ void __launch_bounds__(NT, MINB)
 force_kernel(const __grid_constant__ StepParams p) {
+    static_assert(NT == kGroupBodies, "a target slice r of a CTA is exactly one group of the next generation");
+    static_assert(kGroupBodies % CH == 0, "flush chunks must not straddle groups");
     constexpr int IT = NT * R;
     constexpr int kRecPerTile = kTileBodies;  // float4 records per tile (2 per body pair)
     constexpr uint32_t kTileBytes = kTileBodies * 16;
     constexpr int kWarps = NT / 32;
+    constexpr int kChunksPerGroup = kGroupBodies / CH;
+    typedef Target<POT, EQM, D2, PONLY> Tg;
 
     __shared__ alignas(128) float4 ring[kStages][kRecPerTile];
+    __shared__ alignas(16) GroupHdr ring_hdr[kStages][kGroupsPerTile];
     __shared__ alignas(8) uint64_t full_bar[kStages];
     __shared__ alignas(8) uint64_t empty_bar[kStages];
+    __shared__ double tpos[3][IT];  // FP64 positions of this CTA's targets in packed units (x * 2^-e, exact);
+                                    // re-used by the epilogue for the rows' next positions
+    __shared__ float tmass[IT];
+    __shared__ unsigned char tatt[IT];
     __shared__ double red[kWarps][kDiagValues];
     __shared__ float red_ext[kWarps];
+    __shared__ float sbox[kWarps][6];
     __shared__ int is_last;
 
     const int tid = threadIdx.x;
     const long long unit = blockIdx.x;
     const long long it = unit / p.nseg;
     const int js = (int)(unit - it * p.nseg);
-    const long long i0 = p.i_lo + it * IT;
+    const long long row0 = p.i_lo + it * IT;  // first stream row of the target tile
+    const int li0 = (tid >> 5) * (32 * R) + (tid & 31);  // tile-local row of target r: li0 + 32 * r
+    const long long rbase = row0 + li0;
 
     // scales of the generation being read and of the one the epilogue packs (common.cuh)
-    Scale cur = scale_for(p.extent[(p.gen + kExtentSlots - 1) % kExtentSlots], p.mass_exp, p.g, p.softening);
+    Scale cur = scale_for(p.extent[p.slot_cur], p.mass_exp, p.g, p.softening);
+    if (PONLY && !(p.softening > 0.f)) cur.eps2 = 0.f;  // compute_diagnostics: eps = 0 stays 0 (Physics.hpp:152)
     cur.acc_unit *= p.eqm_mass;
     cur.pot_unit *= p.eqm_mass;
 
     // ---- targets ---------------------------------------------------------------------
-    Target<PACKED, POT, EQM, D2> tg[R];
-    long long ti[R];
+    Tg tg[R];
     double S[R][4];
+    unsigned valid_mask = 0;  // bit r: row row0 + r*NT + tid is a target of this rank
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const long long i = i0 + (long long)r * NT + tid;
-        ti[r] = i < p.i_hi ? i : -1;
-        const long long ic = i < p.i_hi ? i : p.i_hi - 1;
-        const float* rec = p.pk_cur + (ic >> 1) * 8 + (ic & 1);
-        tg[r].init(rec[0], rec[2], rec[4]);
+        const long long row = rbase + 32 * r;
+        const bool ok = row < p.i_hi;
+        if (ok) valid_mask |= 1u << r;
+        const long long body = ok ? (long long)p.order[row] : -1;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = ok ? __dmul_rn(p.x[k][body], cur.inv_len) : 0.0;
+        tg[r].reset();
         S[r][0] = S[r][1] = S[r][2] = S[r][3] = 0.0;
     }
 
@@ -68,6 +91,12 @@ force_kernel(const __grid_constant__ StepParams p) {
     const long long t_begin = p.j_tile_lo + span * js / p.nseg;
     const long long t_end = p.j_tile_lo + span * (js + 1) / p.nseg;
     auto phys = [&](long long t) { return t >= p.hole_lo ? t + p.hole_len : t; };
+    auto issue = [&](int s, long long t) {
+        const long long pt = phys(t);
+        mbar_arrive_expect_tx(&full_bar[s], kTileBytes + kHdrBytesPerTile);
+        tma_load_1d(&ring[s][0], p.pk_cur + pt * (kTileBodies * 4), kTileBytes, &full_bar[s]);
+        tma_load_1d(&ring_hdr[s][0], p.hdr_cur + pt * kGroupsPerTile, kHdrBytesPerTile, &full_bar[s]);
+    };
 
     if (tid == 0) {
 #pragma unroll
@@ -77,64 +106,116 @@ force_kernel(const __grid_constant__ StepParams p) {
         }
         fence_mbar_init();
     }
-    __syncthreads();
+    __syncthreads();  // barriers initialised, tpos filled
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < kStages; ++s) {
-            if (t_begin + s < t_end) {
-                mbar_arrive_expect_tx(&full_bar[s], kTileBytes);
-                tma_load_1d(&ring[s][0], p.pk_cur + phys(t_begin + s) * (kTileBodies * 4), kTileBytes, &full_bar[s]);
-            }
-        }
+        for (int s = 0; s < kStages; ++s)
+            if (t_begin + s < t_end) issue(s, t_begin + s);
     }
 
-    // No CTA-wide barrier in the tile loop: each warp releases a stage through its `empty`
-    // mbarrier, and the producer thread refills the stage released one tile earlier, so it only
-    // ever waits for a warp that has fallen a whole tile behind.
     for (long long t = t_begin; t < t_end; ++t) {
         const int k = (int)(t - t_begin);
         const int s = k % kStages;
         mbar_wait(&full_bar[s], (uint32_t)((k / kStages) & 1));
         const long long j_tile = phys(t) * kTileBodies;
-        const bool diag_tile = POT && (j_tile < i0 + IT) && (j_tile + kTileBodies > i0);
+        const bool diag_tile = POT && (j_tile < row0 + IT) && (j_tile + kTileBodies > row0);
 #pragma unroll 1
-        for (int c = 0; c < kTileBodies / CH; ++c) {
-            const float4* rec = &ring[s][c * CH];
-            const long long j_first = j_tile + c * CH;
-            if (diag_tile)
-                chunk_interact<R, PACKED, POT, true, CH, EQM, D2>(tg, rec, cur.eps2, j_first, ti);
-            else
-                chunk_interact<R, PACKED, POT, false, CH, EQM, D2>(tg, rec, cur.eps2, j_first, ti);
+        for (int g = 0; g < kGroupsPerTile; ++g) {
+            // ---- re-base the targets on this group's origin; near test ---------------------
+            const GroupHdr* gh = &ring_hdr[s][g];
+            const double c0 = gh->c[0], c1 = gh->c[1], c2 = gh->c[2];
+            const float4 hb = *reinterpret_cast<const float4*>(gh->h);  // {hx, hy, hz, reach}
+            bool near = false;
+#ifdef NB_EXP_GROUP_ONCE  // developer A/B only: what the per-group re-basing costs (wrong numerics)
+            if (g == 0)
+#endif
 #pragma unroll
-            for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+            for (int r = 0; r < R; ++r) {
+                const float f0 = (float)__dadd_rn(tpos[0][li0 + 32 * r], -c0);
+                const float f1 = (float)__dadd_rn(tpos[1][li0 + 32 * r], -c1);
+                const float f2v = D2 ? 0.f : (float)__dadd_rn(tpos[2][li0 + 32 * r], -c2);
+                tg[r].set_offset(f0, f1, f2v);
+                const bool inside = (fabsf(f0) < hb.x + hb.w) && (fabsf(f1) < hb.y + hb.w) &&
+                                    (D2 || fabsf(f2v) < hb.z + hb.w);
+                near = near || (inside && ((valid_mask >> r) & 1u));
+            }
+            const float4* grec = &ring[s][g * kGroupBodies];
+            const long long j_group = j_tile + (long long)g * kGroupBodies;
+#ifdef NB_EXP_NO_NEAR  // developer A/B only: what the near path costs (wrong numerics for near pairs)
+            near = false;
+#endif
+            const bool near_any = __any_sync(0xffffffffu, near);
+            if (p.stats && (tid & 31) == 0) {  // developer counters (nb_near_stats): warp x group visits, near ones
+                atomicAdd(&p.stats[0], 1ull);
+                if (near_any) atomicAdd(&p.stats[1], 1ull);
+            }
+            if (!near_any) {
+#pragma unroll 1
+                for (int c = 0; c < kChunksPerGroup; ++c) {
+                    const float4* rec = grec + c * CH;
+                    const long long j_first = j_group + c * CH;
+                    if (diag_tile)
+                        chunk_interact<R, POT, true, CH, EQM, D2, PONLY, 32>(tg, rec, cur.eps2, j_first, rbase);
+                    else
+                        chunk_interact<R, POT, false, CH, EQM, D2, PONLY, 32>(tg, rec, cur.eps2, j_first, rbase);
+#pragma unroll
+                    for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+                }
+            } else {
+                // ---- near group: two-float offsets on both sides, one target at a time -------
+                const float4* glo = reinterpret_cast<const float4*>(p.lo_cur) + j_group;
+#pragma unroll 1
+                for (int c = 0; c < kChunksPerGroup; ++c) {
+                    const float4* rec = grec + c * CH;
+                    const float4* lrec = glo + c * CH;
+                    const long long j_first = j_group + c * CH;
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        float nl[3];
+#pragma unroll
+                        for (int q = 0; q < 3; ++q) {
+                            const double cq = q == 0 ? c0 : (q == 1 ? c1 : c2);
+                            const double d = __dadd_rn(tpos[q][li0 + 32 * r], -cq);
+                            const float fh = (float)d;
+                            nl[q] = -(float)__dadd_rn(d, -(double)fh);
+                        }
+                        const f2 nxl = f2_make(nl[0], nl[0]), nyl = f2_make(nl[1], nl[1]), nzl = f2_make(nl[2], nl[2]);
+                        const long long row = rbase + 32 * r;
+                        if (diag_tile)
+                            chunk_interact_near<POT, true, CH, EQM, D2, PONLY>(tg[r], rec, lrec, nxl, nyl, nzl, cur.eps2,
+                                                                               j_first, row);
+                        else
+                            chunk_interact_near<POT, false, CH, EQM, D2, PONLY>(tg[r], rec, lrec, nxl, nyl, nzl, cur.eps2,
+                                                                                j_first, row);
+                        tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+                    }
+                }
+            }
         }
 #if NB_RING_SYNC
         __syncthreads();  // every warp is done with stage s
-        if (tid == 0 && t + kStages < t_end) {
-            mbar_arrive_expect_tx(&full_bar[s], kTileBytes);
-            tma_load_1d(&ring[s][0], p.pk_cur + phys(t + kStages) * (kTileBodies * 4), kTileBytes, &full_bar[s]);
-        }
+        if (tid == 0 && t + kStages < t_end) issue(s, t + kStages);
 #else
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty_bar[s]);
         if (tid == 0 && k >= 1 && t - 1 + kStages < t_end) {
             const int sp = (k - 1) % kStages;
             mbar_wait(&empty_bar[sp], (uint32_t)(((k - 1) / kStages) & 1));
-            mbar_arrive_expect_tx(&full_bar[sp], kTileBytes);
-            tma_load_1d(&ring[sp][0], p.pk_cur + phys(t - 1 + kStages) * (kTileBodies * 4), kTileBytes, &full_bar[sp]);
+            issue(sp, t - 1 + kStages);
         }
 #endif
     }
 
     // ---- combine source segments (fixed order) ------------------------------------------
     constexpr int NC = POT ? 4 : 3;
+    constexpr int C0 = PONLY ? 3 : 0;  // potential-only kernels carry S[3] alone
     if (p.nseg > 1) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (ti[r] < 0) continue;
-            const long long col = ti[r] - p.i_lo;
+            if (!((valid_mask >> r) & 1u)) continue;
+            const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) __stcg(&p.part[((long long)(1 + js) * 4 + c) * p.i_cap + col], S[r][c]);
+            for (int c = C0; c < NC; ++c) __stcg(&p.part[((long long)(1 + js) * 4 + c) * p.i_cap + col], S[r][c]);
         }
         __threadfence();
         __syncthreads();
@@ -148,10 +229,10 @@ force_kernel(const __grid_constant__ StepParams p) {
         __threadfence();
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (ti[r] < 0) continue;
-            const long long col = ti[r] - p.i_lo;
+            if (!((valid_mask >> r) & 1u)) continue;
+            const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) {
+            for (int c = C0; c < NC; ++c) {
                 double acc = 0.0;
                 for (int sgm = 0; sgm < p.nseg; ++sgm) acc += __ldcg(&p.part[((long long)(1 + sgm) * 4 + c) * p.i_cap + col]);
                 S[r][c] = acc;
@@ -161,36 +242,59 @@ force_kernel(const __grid_constant__ StepParams p) {
     if (p.accumulate) {  // partial sums left by an earlier launch over other sources
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (ti[r] < 0) continue;
-            const long long col = ti[r] - p.i_lo;
+            if (!((valid_mask >> r) & 1u)) continue;
+            const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) S[r][c] += __ldcg(&p.part[(long long)c * p.i_cap + col]);
+            for (int c = C0; c < NC; ++c) S[r][c] += __ldcg(&p.part[(long long)c * p.i_cap + col]);
         }
     }
     if (p.mode == kPartialOnly) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (ti[r] < 0) continue;
-            const long long col = ti[r] - p.i_lo;
+            if (!((valid_mask >> r) & 1u)) continue;
+            const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
-            for (int c = 0; c < NC; ++c) p.part[(long long)c * p.i_cap + col] = S[r][c];
+            for (int c = C0; c < NC; ++c) p.part[(long long)c * p.i_cap + col] = S[r][c];
         }
         return;
     }
 
     // ---- epilogue -----------------------------------------------------------------------
-    const Scale nxt = scale_for(p.extent[p.gen % kExtentSlots], p.mass_exp, p.g, p.softening);
+    const Scale nxt = scale_for(p.extent[p.slot_nxt], p.mass_exp, p.g, p.softening);
     const double inv_mass = pow2d(-p.mass_exp);
+    const bool packs = (p.mode == kEuler || p.mode == kVerletKickDrift);
     DiagTerms dg;
 #pragma unroll
     for (int k = 0; k < kDiagValues; ++k) dg.v[k] = 0.0;
     float ext = 0.f;
+    if (packs) __syncthreads();  // every warp is done reading tpos
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        if (ti[r] < 0) continue;
-        ext = fmaxf(ext, body_epilogue<POT>(p, ti[r], S[r], cur, nxt, inv_mass, dg));
+        NextRow nx;
+        nx.x[0] = nx.x[1] = nx.x[2] = 0.0;
+        nx.m = 0.f;
+        nx.attracts = false;
+        if ((valid_mask >> r) & 1u) body_epilogue<POT>(p, (long long)p.order[rbase + 32 * r], S[r], cur, dg, nx);
+        if (packs) {  // hand the row's next position to the pack below (which groups rows by 128, not by warp)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = nx.x[k];
+            tmass[li0 + 32 * r] = nx.m;
+            tatt[li0 + 32 * r] = nx.attracts ? 1 : 0;
+        }
     }
-    const bool packs = (p.mode == kEuler || p.mode == kVerletKickDrift);
+    if (packs) {
+        __syncthreads();
+        // slice q of the tile (rows row0 + q*NT + tid) is exactly one group of generation gen+1
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            if (row0 + (long long)q * NT >= p.row_cap) break;  // CTA-uniform
+            const double nx3[3] = {tpos[0][q * NT + tid], tpos[1][q * NT + tid], tpos[2][q * NT + tid]};
+            const bool att = tatt[q * NT + tid] != 0;
+            ext = fmaxf(ext, extent_of(nx3, att));
+            pack_group<NT>(p.pk_next, p.lo_next, p.hdr_next, row0 + (long long)q * NT + tid, nx3, tmass[q * NT + tid], att,
+                           nxt.inv_len, inv_mass, sbox);
+        }
+    }
     if (packs) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) ext = fmaxf(ext, __shfl_xor_sync(0xffffffffu, ext, o));

@@ -127,59 +127,48 @@ constexpr int kCtaScale = kNT / 128;
 typedef void (*ForceFn)(const StepParams);
 
 struct KernelEntry {
-    int r, packed, pot, chunk, minb, eqm, d2;
+    int r, kind, eqm, d2;  // kind: 0 force, 1 force + potential, 2 potential only
     ForceFn fn;
 };
 
-#define NB_K(R, P, POT, MINB, CH) {R, P, POT, CH, MINB, 0, 0, force_kernel<kNT, R, (P) != 0, (POT) != 0, (MINB) / kCtaScale, CH>}
-// specialised packed force-only kernels: E uniform mass (no m*w multiply), D z == 0 (reference 2-D uploads)
-#define NB_KS(R, E, D) {R, 1, 0, 64, 4, E, D, force_kernel<kNT, R, true, false, 4 / kCtaScale, 64, (E) != 0, (D) != 0>}
-#define NB_KSP(R, E, D) {R, 1, 1, 64, 4, E, D, force_kernel<kNT, R, true, true, 4 / kCtaScale, 64, (E) != 0, (D) != 0>}
+// <threads, R, POT, CTAs/SM, flush chunk, EQM uniform mass (no m*w multiply), D2 z == 0 (reference 2-D uploads), PONLY>
+#define NB_KF(R, E, D) {R, 0, E, D, force_kernel<kNT, R, false, 4 / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
+// the potential accumulators of R >= 3 targets do not fit 128 registers: those variants run 3 CTAs per SM
+#define NB_KP(R, E, D) {R, 1, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
+#define NB_KD(R, E, D) {R, 2, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, true>}
+#define NB_ALL_ED(M, R) M(R, 0, 0), M(R, 1, 0), M(R, 0, 1), M(R, 1, 1)
 const KernelEntry kKernels[] = {
-    // production set: flush chunk kFlushChunk (64), 4 CTAs/SM
-    NB_K(4, 1, 0, 4, 64), NB_K(2, 1, 0, 4, 64), NB_K(1, 1, 0, 4, 64),
-    NB_K(4, 0, 0, 4, 64), NB_K(2, 0, 0, 4, 64), NB_K(1, 0, 0, 4, 64),
-    NB_K(2, 1, 1, 4, 64), NB_K(1, 1, 1, 4, 64), NB_K(2, 0, 1, 4, 64), NB_K(1, 0, 1, 4, 64),
-    // tuning set (NB_FORCE_CHUNK)
-    NB_K(4, 1, 0, 4, 32), NB_K(4, 1, 0, 4, 128), NB_K(3, 1, 0, 4, 64),
-    NB_KS(4, 1, 0), NB_KS(3, 1, 0), NB_KS(2, 1, 0), NB_KS(1, 1, 0),
-    NB_KS(4, 0, 1), NB_KS(3, 0, 1), NB_KS(2, 0, 1), NB_KS(1, 0, 1),
-    NB_KS(4, 1, 1), NB_KS(3, 1, 1), NB_KS(2, 1, 1), NB_KS(1, 1, 1),
+    NB_ALL_ED(NB_KF, 4), NB_ALL_ED(NB_KF, 3), NB_ALL_ED(NB_KF, 2), NB_ALL_ED(NB_KF, 1),
     // with the fused potential (nb_step_with_diagnostics)
-    NB_KSP(3, 0, 0), NB_KSP(3, 1, 0), NB_KSP(2, 1, 0), NB_KSP(1, 1, 0), NB_KSP(3, 0, 1), NB_KSP(2, 0, 1), NB_KSP(1, 0, 1),
-    NB_KSP(3, 1, 1), NB_KSP(2, 1, 1), NB_KSP(1, 1, 1),
+    NB_ALL_ED(NB_KP, 4), NB_ALL_ED(NB_KP, 3), NB_ALL_ED(NB_KP, 2), NB_ALL_ED(NB_KP, 1),
+    // potential only (nb_compute_diagnostics, hot loop B)
+    NB_ALL_ED(NB_KD, 4), NB_ALL_ED(NB_KD, 2), NB_ALL_ED(NB_KD, 1),
 };
-#undef NB_K
-#undef NB_KS
-#undef NB_KSP
+#undef NB_KF
+#undef NB_KP
+#undef NB_KD
+#undef NB_ALL_ED
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
 
-const KernelEntry* find_kernel(int r, int packed, int pot, int chunk = kFlushChunk, int minb = 4, int eqm = 0,
-                               int d2 = 0) {
+const KernelEntry* find_kernel(int r, int kind, int eqm, int d2) {
     for (int k = 0; k < kNumKernels; ++k)
-        if (kKernels[k].r == r && kKernels[k].packed == packed && kKernels[k].pot == pot && kKernels[k].chunk == chunk &&
-            kKernels[k].minb == minb && kKernels[k].eqm == eqm && kKernels[k].d2 == d2)
+        if (kKernels[k].r == r && kKernels[k].kind == kind && kKernels[k].eqm == eqm && kKernels[k].d2 == d2)
             return &kKernels[k];
     return nullptr;
 }
 
 // Choose targets-per-thread and the source split so the grid fills whole waves of SMs.
-LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles, bool pot) {
+// kind: 0 force, 1 force + potential, 2 potential only (stand-alone diagnostics stream).
+LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles, int kind) {
     LaunchPlan best;
     double best_score = -1.0;
-    const int packed = c->forced_packed >= 0 ? c->forced_packed : 1;
-    const int r_opts_force[] = {4, 3, 2, 1};
-    const int r_opts_pot[] = {3, 2, 1};
-    const int* r_opts = pot ? r_opts_pot : r_opts_force;
-    const int n_opts = pot ? 3 : 4;
-    for (int q = 0; q < n_opts; ++q) {
+    const int r_opts[] = {4, 3, 2, 1};
+    for (int q = 0; q < 4; ++q) {
         const int r = r_opts[q];
-        if (c->forced_r && c->forced_r != r && !(pot && c->forced_r > 3 && r == 3)) continue;
-        // the specialised variants exist for the production shape only (packed, chunk 64, 4 CTAs/SM)
-        const bool special = packed == 1 && (pot || (c->forced_chunk == kFlushChunk && c->forced_minb == 4));
-        const int eqm = special && c->uniform_mass ? 1 : 0, d2 = special && c->planar ? 1 : 0;
-        const KernelEntry* ke = pot ? find_kernel(r, packed, 1, kFlushChunk, 4, eqm, d2)
-                                    : find_kernel(r, packed, 0, c->forced_chunk, c->forced_minb, eqm, d2);
+        if (c->forced_r && c->forced_r != r) continue;
+        // the stand-alone diagnostics count every body: its uniform-mass variant needs ALL masses equal
+        const int eqm = (kind == 2 ? c->diag_uniform_mass : c->uniform_mass) ? 1 : 0, d2 = c->planar ? 1 : 0;
+        const KernelEntry* ke = find_kernel(r, kind, eqm, d2);
         if (!ke) continue;
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
@@ -254,11 +243,18 @@ __global__ void __launch_bounds__(256) fill_far_kernel(float* pk, long long n_pa
 inline unsigned int blocks_for(long long n, int threads) { return (unsigned int)std::max<long long>(1, (n + threads - 1) / threads); }
 
 void free_bodies(nb_ctx* c) {
-    cudaFree(c->state); cudaFree(c->mass); cudaFree(c->pinned); cudaFree(c->live);
-    cudaFree(c->pk[0]); cudaFree(c->pk[1]); cudaFree(c->part); cudaFree(c->tile_counter);
-    cudaFree(c->diag_part); cudaFree(c->dpk); cudaFree(c->staging);
-    c->state = nullptr; c->mass = nullptr; c->pinned = c->live = nullptr; c->pk[0] = c->pk[1] = nullptr;
-    c->part = nullptr; c->tile_counter = nullptr; c->diag_part = nullptr; c->dpk = nullptr; c->staging = nullptr;
+    cudaFree(c->state); cudaFree(c->mass); cudaFree(c->pinned); cudaFree(c->order);
+    cudaFree(c->part); cudaFree(c->tile_counter); cudaFree(c->diag_part); cudaFree(c->staging);
+    cudaFree(c->dpk); cudaFree(c->dpk_lo); cudaFree(c->dhdr); cudaFree(c->sort_tmp);
+    for (int g = 0; g < 2; ++g) {
+        cudaFree(c->live2[g]); cudaFree(c->pk[g]); cudaFree(c->pk_lo[g]); cudaFree(c->hdr[g]);
+        cudaFree(c->sort_keys[g]); cudaFree(c->sort_vals[g]);
+        c->live2[g] = nullptr; c->pk[g] = c->pk_lo[g] = nullptr; c->hdr[g] = nullptr;
+        c->sort_keys[g] = nullptr; c->sort_vals[g] = nullptr;
+    }
+    c->state = nullptr; c->mass = nullptr; c->pinned = nullptr; c->order = nullptr;
+    c->part = nullptr; c->tile_counter = nullptr; c->diag_part = nullptr; c->staging = nullptr;
+    c->dpk = c->dpk_lo = nullptr; c->dhdr = nullptr; c->sort_tmp = nullptr; c->sort_tmp_bytes = 0;
     c->cap = 0; c->staging_bytes = 0; c->part_slots = 0; c->i_cap = 0; c->counter_cap = 0; c->diag_part_rows = 0;
 }
 
@@ -282,36 +278,65 @@ int size_for(nb_ctx* c, long long n) {
     c->lo = lo;
     c->hi = hi;
     c->n = n;
+    c->x_sel = 0;
     const long long rows = c->n_tiles * kTileBodies;
+    const long long groups = rows / kGroupBodies;
     if (rows > c->cap) {
         free_bodies(c);
-        NB_CUDA(cudaMalloc(&c->state, sizeof(double) * 12 * rows));
+        NB_CUDA(cudaMalloc(&c->state, sizeof(double) * 15 * rows));
         NB_CUDA(cudaMalloc(&c->mass, sizeof(float) * rows));
         NB_CUDA(cudaMalloc(&c->pinned, rows));
-        NB_CUDA(cudaMalloc(&c->live, rows));
-        NB_CUDA(cudaMalloc(&c->pk[0], sizeof(float) * 4 * rows));
-        NB_CUDA(cudaMalloc(&c->pk[1], sizeof(float) * 4 * rows));
-        NB_CUDA(cudaMalloc(&c->dpk, sizeof(float4) * rows));
+        NB_CUDA(cudaMalloc(&c->order, sizeof(int) * rows));
+        for (int g = 0; g < 2; ++g) {
+            NB_CUDA(cudaMalloc(&c->live2[g], rows));
+            NB_CUDA(cudaMalloc(&c->pk[g], sizeof(float) * 4 * rows));
+            NB_CUDA(cudaMalloc(&c->pk_lo[g], sizeof(float) * 4 * rows));
+            NB_CUDA(cudaMalloc(&c->hdr[g], sizeof(GroupHdr) * groups));
+        }
+        NB_CUDA(cudaMalloc(&c->dpk, sizeof(float) * 4 * rows));
+        NB_CUDA(cudaMalloc(&c->dpk_lo, sizeof(float) * 4 * rows));
+        NB_CUDA(cudaMalloc(&c->dhdr, sizeof(GroupHdr) * groups));
+        // Hilbert sort of this rank's rows (cub radix sort, double-buffered keys / values)
+        const long long per_rank = c->tiles_per_rank * kTileBodies;
+        for (int g = 0; g < 2; ++g) {
+            NB_CUDA(cudaMalloc(&c->sort_keys[g], sizeof(unsigned long long) * per_rank));
+            NB_CUDA(cudaMalloc(&c->sort_vals[g], sizeof(int) * per_rank));
+        }
+        size_t tmp = 0;
+        NB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, c->sort_keys[0], c->sort_keys[1], c->sort_vals[0],
+                                                c->sort_vals[1], (int)per_rank, 0, 63, c->stream));
+        NB_CUDA(cudaMalloc(&c->sort_tmp, tmp ? tmp : 16));
+        c->sort_tmp_bytes = tmp;
         c->cap = rows;
     }
-    NB_CUDA(cudaMemsetAsync(c->state, 0, sizeof(double) * 12 * c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->state, 0, sizeof(double) * 15 * c->cap, c->stream));
     NB_CUDA(cudaMemsetAsync(c->mass, 0, sizeof(float) * c->cap, c->stream));
     NB_CUDA(cudaMemsetAsync(c->pinned, 0, c->cap, c->stream));
-    NB_CUDA(cudaMemsetAsync(c->live, 0, c->cap, c->stream));
-    // every row starts as a non-attracting row (x = kFarPacked, m = 0); padding rows stay that way
-    for (int g = 0; g < 2; ++g)
+    // every row starts as a non-attracting row (hi_x = kFarPacked, m = 0) of a group that is never "near";
+    // padding rows stay that way
+    for (int g = 0; g < 2; ++g) {
+        NB_CUDA(cudaMemsetAsync(c->live2[g], 0, c->cap, c->stream));
+        NB_CUDA(cudaMemsetAsync(c->pk_lo[g], 0, sizeof(float) * 4 * c->cap, c->stream));
+        NB_CUDA(cudaMemsetAsync(c->hdr[g], 0, sizeof(GroupHdr) * (c->cap / kGroupBodies), c->stream));
         fill_far_kernel<<<blocks_for(c->cap / 2, 256), 256, 0, c->stream>>>(c->pk[g], c->cap / 2);
+    }
+    NB_CUDA(cudaMemsetAsync(c->dpk_lo, 0, sizeof(float) * 4 * c->cap, c->stream));
+    NB_CUDA(cudaMemsetAsync(c->dhdr, 0, sizeof(GroupHdr) * (c->cap / kGroupBodies), c->stream));
+    fill_far_kernel<<<blocks_for(c->cap / 2, 256), 256, 0, c->stream>>>(c->dpk, c->cap / 2);
+    iota_order_kernel<<<blocks_for(c->cap, kStateThreads), kStateThreads, 0, c->stream>>>(c->order, 0, c->cap);
     NB_CUDA(cudaGetLastError());
-    c->kernel_launches += 2;
+    c->kernel_launches += 4;
+    c->order_valid = false;
+    c->packs_since_sort = 0;
 
     // launch plans: all sources in one launch, or (sharded) own sources first, the rest after the exchange
     const long long n_local = c->hi - c->lo;
     int slots = 1;
-    for (int pot = 0; pot < 2; ++pot) {
-        c->plans[0][pot] = make_plan(c, n_local, c->n_tiles, pot != 0);
-        c->plans[1][pot] = make_plan(c, n_local, c->tiles_per_rank, pot != 0);
-        c->plans[2][pot] = make_plan(c, n_local, std::max<long long>(1, c->n_tiles - c->tiles_per_rank), pot != 0);
-        for (int w = 0; w < 3; ++w) slots = std::max(slots, c->plans[w][pot].nseg);
+    for (int kind = 0; kind < 3; ++kind) {
+        c->plans[0][kind] = make_plan(c, n_local, c->n_tiles, kind);
+        c->plans[1][kind] = make_plan(c, n_local, c->tiles_per_rank, kind);
+        c->plans[2][kind] = make_plan(c, n_local, std::max<long long>(1, c->n_tiles - c->tiles_per_rank), kind);
+        for (int w = 0; w < 3; ++w) slots = std::max(slots, c->plans[w][kind].nseg);
     }
     const long long i_cap = ((std::max<long long>(n_local, 1) + 1023) / 1024) * 1024;
     if (slots > c->part_slots || i_cap > c->i_cap) {
@@ -391,6 +416,12 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     NB_CUDA(cudaEventCreate(&c->ev_timer1));
     NB_CUDA(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     NB_CUDA(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
+    for (int g = 0; g < 2; ++g) {
+        NB_CUDA(cudaEventCreate(&c->ev_comm0[g]));
+        NB_CUDA(cudaEventCreate(&c->ev_comm1[g]));
+    }
+    NB_CUDA(cudaEventCreate(&c->ev_own0));
+    NB_CUDA(cudaEventCreate(&c->ev_own1));
     NB_CUDA(cudaMalloc(&c->extent, sizeof(unsigned int) * (kExtentSlots + 4)));
     NB_CUDA(cudaMemset(c->extent, 0, sizeof(unsigned int) * (kExtentSlots + 4)));
     // [0,16): this rank's fixed-order sums; [16, 16 + kDiagValues * world): every rank's, all-gathered
@@ -398,10 +429,8 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * totals_len));
     NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * totals_len));
     if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
-    if (const char* v = getenv("NB_FORCE_PACKED")) c->forced_packed = atoi(v);
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
-    if (const char* v = getenv("NB_FORCE_CHUNK")) c->forced_chunk = atoi(v);
-    if (const char* v = getenv("NB_FORCE_MINB")) c->forced_minb = atoi(v);
+    if (const char* v = getenv("NB_RESORT_EVERY")) c->resort_every = std::max(1, atoi(v));
     if (const char* v = getenv("NB_FORCE_GENERIC")) c->force_generic = atoi(v) != 0;
     *out = c;
     return NB_OK;
@@ -443,6 +472,7 @@ extern "C" void nb_destroy(nb_ctx* c) {
     cudaFree(c->collide_scratch);
     cudaFree(c->bh_scratch);
     cudaFree(c->merge_scratch);
+    cudaFree(c->near_stats);
     if (c->h_merge) cudaFreeHost(c->h_merge);
     if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
     cudaFree(c->totals);
@@ -452,6 +482,12 @@ extern "C" void nb_destroy(nb_ctx* c) {
     cudaEventDestroy(c->ev_timer1);
     cudaEventDestroy(c->ev_packed);
     cudaEventDestroy(c->ev_gathered);
+    for (int g = 0; g < 2; ++g) {
+        cudaEventDestroy(c->ev_comm0[g]);
+        cudaEventDestroy(c->ev_comm1[g]);
+    }
+    cudaEventDestroy(c->ev_own0);
+    cudaEventDestroy(c->ev_own1);
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->comm_stream);
     delete c;
@@ -463,7 +499,10 @@ extern "C" int nb_set_config(nb_ctx* c, const nb_config* cfg) {
         return fail(NB_ERR_INVALID, "nb_set_config: integrator must be 0 (Euler) or 1 (Verlet)");
     const bool repack = cfg->softening != c->cfg.softening || cfg->g != c->cfg.g;
     c->cfg = *cfg;
-    if (repack) c->acc_valid = false;  // accelerations depend on G and epsilon
+    if (repack) {  // accelerations depend on G and epsilon, and so does the drift prepared with them
+        c->acc_valid = false;
+        c->drop_speculation();
+    }
     return NB_OK;
 }
 
@@ -505,22 +544,50 @@ extern "C" int nb_substep_plan(float dt, float max_substep, int32_t max_substeps
 // ---------------------------------------------------------------------------------------
 namespace {
 
-// All-gather generation `gen`'s j-stream slices in place and max-reduce the rotating extent
-// slots, on the comm stream, after everything enqueued so far on the main stream.
+// All-gather generation `gen`'s j-stream slices (hi parts, residuals, group headers) in place and
+// max-reduce the rotating extent slot, on the comm stream, after everything enqueued so far on the main stream.
 int exchange_packed(nb_ctx* c, int gen, bool main_waits) {
     if (c->world <= 1) return NB_OK;
     NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
     NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
+    const size_t rows = (size_t)c->tiles_per_rank * kTileBodies;
+    const size_t count = rows * 4;  // floats per rank
+    const size_t hdr_count = rows / kGroupBodies * (sizeof(GroupHdr) / sizeof(float));
     float* buf = c->pk[gen & 1];
-    const size_t count = (size_t)c->tiles_per_rank * kTileBodies * 4;  // floats per rank
+    float* lob = c->pk_lo[gen & 1];
+    float* hdb = reinterpret_cast<float*>(c->hdr[gen & 1]);
+    if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_comm0[gen & 1], c->comm_stream));
     NB_NCCL(g_nccl.GroupStart());
     NB_NCCL(g_nccl.AllGather(buf + (size_t)c->rank * count, buf, count, kNcclFloat32, c->nccl_comm, c->comm_stream));
+    NB_NCCL(g_nccl.AllGather(lob + (size_t)c->rank * count, lob, count, kNcclFloat32, c->nccl_comm, c->comm_stream));
+    NB_NCCL(g_nccl.AllGather(hdb + (size_t)c->rank * hdr_count, hdb, hdr_count, kNcclFloat32, c->nccl_comm,
+                             c->comm_stream));
     // only the slot this generation's epilogue wrote: the others are being read by kernels in flight
     unsigned int* slot = c->extent + (gen % kExtentSlots);
     NB_NCCL(g_nccl.AllReduce(slot, slot, 1, kNcclUint32, kNcclMax, c->nccl_comm, c->comm_stream));
     NB_NCCL(g_nccl.GroupEnd());
+    if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_comm1[gen & 1], c->comm_stream));
     NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
     if (main_waits) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+    return NB_OK;
+}
+
+// Order this rank's stream rows along a Hilbert curve of the current positions (extent slot `slot` holds the
+// cube). Rows of other ranks keep whatever order their owner chose: only the owner reads `order`.
+int sort_stream(nb_ctx* c, int slot) {
+    const long long n_local = c->hi - c->lo;
+    if (n_local <= 0) return NB_OK;
+    if (c->dim == 2)
+        curve_key_kernel<2><<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(
+            c->view(), c->extent, slot, c->sort_keys[0], c->sort_vals[0]);
+    else
+        curve_key_kernel<3><<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(
+            c->view(), c->extent, slot, c->sort_keys[0], c->sort_vals[0]);
+    size_t tmp = c->sort_tmp_bytes;
+    NB_CUDA(cub::DeviceRadixSort::SortPairs(c->sort_tmp, tmp, c->sort_keys[0], c->sort_keys[1], c->sort_vals[0],
+                                            c->order + c->lo, (int)n_local, 0, 63, c->stream));
+    c->kernel_launches += 2;  // + cub's own passes
+    c->sorts++;
     return NB_OK;
 }
 
@@ -528,6 +595,7 @@ int exchange_packed(nb_ctx* c, int gen, bool main_waits) {
 int prepare_packed(nb_ctx* c) {
     const StateView s = c->view();
     c->gen += 1;
+    c->drop_speculation();
     const int g = c->gen;
     NB_CUDA(cudaMemsetAsync(c->extent, 0, sizeof(unsigned int) * kExtentSlots, c->stream));
     const long long n_local = c->hi - c->lo;
@@ -544,9 +612,18 @@ int prepare_packed(nb_ctx* c) {
         NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     }
+    if (!c->order_valid || c->packs_since_sort >= c->resort_every) {
+        // a world of one group gains nothing from an ordering: it keeps upload order (and with it the lane
+        // pairing of the reference's mirror-symmetric three-body seed, whose pulls on the centre then cancel exactly)
+        if (c->n > kGroupBodies) NB_TRY(sort_stream(c, (g + kExtentSlots - 1) % kExtentSlots));
+        c->order_valid = true;
+        c->packs_since_sort = 0;
+    }
     if (n_local > 0) {
-        pack_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(
-            s, c->pk[g & 1], c->extent, g, c->mass_exp, c->cfg.g, c->cfg.softening);
+        const long long groups = (c->tiles_per_rank * kTileBodies) / kGroupBodies;
+        pack_kernel<false><<<(unsigned int)groups, kGroupBodies, 0, c->stream>>>(
+            s, c->order, c->pk[g & 1], c->pk_lo[g & 1], c->hdr[g & 1], c->live2[g & 1], c->extent,
+            (g + kExtentSlots - 1) % kExtentSlots, c->mass_exp, c->cfg.g, c->cfg.softening);
         c->kernel_launches++;
     }
     NB_CUDA(cudaGetLastError());
@@ -575,28 +652,41 @@ int prof_end(nb_ctx* c) {
 }
 
 // One launch of the force kernel. which: 0 all sources, 1 own sources (partial only),
-// 2 remote sources (+ partial from launch 1, + epilogue).
-int launch_force(nb_ctx* c, int which, int mode, bool pot, double dt) {
+// 2 remote sources (+ partial from launch 1, + epilogue). kind: 0 force, 1 force + potential,
+// 2 potential only over the stand-alone diagnostics stream.
+int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
     const long long n_local = c->hi - c->lo;
     if (n_local <= 0) return NB_OK;
-    const LaunchPlan& pl = c->plans[which][pot ? 1 : 0];
+    const LaunchPlan& pl = c->plans[which][kind];
     const KernelEntry& ke = kKernels[pl.variant];
     StepParams p;
     const StateView s = c->view();
     for (int k = 0; k < 3; ++k) {
         p.x[k] = s.x[k]; p.v[k] = s.v[k]; p.a[k] = s.a[k]; p.a0[k] = s.a0[k];
+        p.xs[k] = c->pos_slot(c->x_sel ^ 1, k);
     }
-    p.mass = c->mass; p.pinned = c->pinned; p.live = c->live;
-    p.pk_cur = c->pk[c->gen & 1];
-    p.pk_next = c->pk[(c->gen + 1) & 1];
+    p.mass = c->mass; p.pinned = c->pinned;
+    p.live = c->live2[c->gen & 1];
+    p.live_next = c->live2[(c->gen + 1) & 1];
+    p.order = c->order;
+    if (kind == 2) {
+        p.pk_cur = c->dpk; p.lo_cur = c->dpk_lo; p.hdr_cur = c->dhdr;
+        p.slot_cur = kDiagExtentSlot; p.slot_nxt = kDiagExtentSlot;
+    } else {
+        p.pk_cur = c->pk[c->gen & 1]; p.lo_cur = c->pk_lo[c->gen & 1]; p.hdr_cur = c->hdr[c->gen & 1];
+        p.slot_cur = (c->gen + kExtentSlots - 1) % kExtentSlots; p.slot_nxt = c->gen % kExtentSlots;
+    }
+    p.pk_next = c->pk[(c->gen + 1) & 1]; p.lo_next = c->pk_lo[(c->gen + 1) & 1]; p.hdr_next = c->hdr[(c->gen + 1) & 1];
     p.extent = c->extent;
     p.part = c->part;
     p.tile_counter = c->tile_counter;
     p.diag_part = c->diag_part;
+    p.stats = c->near_stats;
     p.n = c->n;
     p.n_tiles = c->n_tiles;
     p.i_lo = c->lo; p.i_hi = c->hi;
     p.i_cap = c->i_cap;
+    p.row_cap = c->lo + c->tiles_per_rank * kTileBodies;
     const long long own_lo = (long long)c->rank * c->tiles_per_rank;
     p.hole_lo = c->n_tiles; p.hole_len = 0;
     if (which == 0) { p.j_tile_lo = 0; p.j_tile_hi = c->n_tiles; }
@@ -620,33 +710,60 @@ int launch_force(nb_ctx* c, int which, int mode, bool pot, double dt) {
     NB_TRY(prof_end(c));
     c->kernel_launches++;
     c->interactions += (double)n_local * (double)(p.j_tile_hi - p.j_tile_lo) * kTileBodies;
-    if (which != 1 && pot) {
+    if (which != 1 && kind != 0) {
         c->step_diag_rows = n_it;
-        c->step_diag_valid = true;
+        c->step_diag_valid = kind == 1;
     }
     return NB_OK;
 }
 
-// One force evaluation over all sources with epilogue `mode`; advances the generation when
-// the epilogue packed the next j-stream.
-int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
-    if (!c->packed_valid) NB_TRY(prepare_packed(c));
-    const bool packs = (mode == kEuler || mode == kVerletKickDrift);
-    if (c->world > 1 && c->plans[2][0].n_itiles > 0 && c->n_tiles > c->tiles_per_rank) {
-        // own sources need no communication: start on them while the exchange of the
-        // previous epilogue's pack is still in flight, then finish with the remote ones
-        NB_TRY(launch_force(c, 1, mode, pot, dt));
+// Own sources need no communication: in a sharded context a pass starts on them while the exchange of the
+// stream it reads may still be in flight, then finishes with the remote ones.
+int launch_pass(nb_ctx* c, int mode, int kind, double dt) {
+    if (c->world > 1 && c->n_tiles > c->tiles_per_rank) {
+        if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_own0, c->stream));
+        NB_TRY(launch_force(c, 1, mode, kind, dt));
+        if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_own1, c->stream));
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-        NB_TRY(launch_force(c, 2, mode, pot, dt));
+        NB_TRY(launch_force(c, 2, mode, kind, dt));
     } else {
-        NB_TRY(launch_force(c, 0, mode, pot, dt));
-    }
-    c->force_evals++;
-    if (packs) {
-        c->gen += 1;
-        NB_TRY(exchange_packed(c, c->gen, false));  // consumed by the next pass after its own-sources launch
+        NB_TRY(launch_force(c, 0, mode, kind, dt));
     }
     return NB_OK;
+}
+
+// One force evaluation over all sources with epilogue `mode`. kEuler commits the generation its epilogue
+// packed; kVerletKickDrift leaves it speculative (commit_drift()).
+int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
+    if (!c->packed_valid) NB_TRY(prepare_packed(c));
+    // a plain re-evaluation at the same positions through the same kernel reproduces Acceleration bit for
+    // bit and leaves a prepared drift usable; anything else (another kernel variant, a move) does not
+    if (!(mode == kForceOnly && !pot && c->spec_kind == 0)) c->drop_speculation();
+    NB_TRY(launch_pass(c, mode, pot ? 1 : 0, dt));
+    c->force_evals++;
+    if (mode == kEuler) {
+        c->gen += 1;
+        c->packs_since_sort++;
+        NB_TRY(exchange_packed(c, c->gen, false));  // consumed by the next pass after its own-sources launch
+        if (c->packs_since_sort >= c->resort_every) c->packed_valid = false;  // next pass re-sorts and re-packs
+    } else if (mode == kVerletKickDrift) {
+        c->spec_valid = true;
+        c->spec_h = dt;
+        c->spec_kind = pot ? 1 : 0;
+        NB_TRY(exchange_packed(c, c->gen + 1, false));
+    }
+    return NB_OK;
+}
+
+// The drift the last kick epilogue prepared becomes the state: Position <- shadow positions, generation + 1
+// (its j-stream, group headers, gather-filter flags and extent slot were written by that epilogue).
+void commit_drift(nb_ctx* c) {
+    c->x_sel ^= 1;
+    c->gen += 1;
+    c->packs_since_sort++;
+    c->spec_valid = false;
+    c->step_diag_valid = false;  // the fused potential described the positions before this drift
+    if (c->packs_since_sort >= c->resort_every) c->packed_valid = false;  // this pass re-sorts and re-packs
 }
 
 }  // namespace
@@ -665,19 +782,23 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
     // kernel specialisations (NB_FORCE_GENERIC=1 disables them): one common mass over every body that can
     // ever pass the gather filter, and z == 0 for reference-layout (2-D) uploads
     float m0 = 0.f;
-    bool uniform = n > 0;
+    bool uniform = n > 0, every = true;
     for (int64_t i = 0; i < n && uniform; ++i) {
         const float m = mass[i];
-        if (!(m > 0.f && m <= 3.4028234663852886e38f)) continue;  // never live, Physics.hpp:198-199
+        if (!(m > 0.f && m <= 3.4028234663852886e38f)) {  // never live, Physics.hpp:198-199
+            every = false;
+            continue;
+        }
         if (m0 == 0.f) m0 = m;
         uniform = (m == m0);
     }
     c->uniform_mass = uniform && m0 > 0.f && !c->force_generic;
+    c->diag_uniform_mass = c->uniform_mass && every;  // compute_diagnostics sums over ALL bodies
     c->uniform_packed_mass = (double)m0 * pow2d(-c->mass_exp);
     c->planar = dim == 2 && !c->force_generic;
     NB_TRY(size_for(c, n));
     c->acc_valid = false;
-    c->packed_valid = false;
+    c->packed_valid = false; c->drop_speculation();
     c->step_diag_valid = false;
     if (n == 0) return NB_OK;
     // a rank only needs the FP64 state of its own targets: the other bodies reach it as FP32 sources
@@ -842,7 +963,7 @@ static int exact_verlet(nb_ctx* c, double h, long long n_sub) {
         c->kernel_launches += 2;
     }
     NB_CUDA(cudaGetLastError());
-    c->packed_valid = false;
+    c->packed_valid = false; c->drop_speculation();
     return NB_OK;
 }
 
@@ -850,7 +971,7 @@ static int exact_euler_move(nb_ctx* c, double h) {
     euler_move_kernel<<<blocks_for(c->n, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h, c->cfg.max_speed);
     NB_CUDA(cudaGetLastError());
     c->kernel_launches++;
-    c->packed_valid = false;
+    c->packed_valid = false; c->drop_speculation();
     return NB_OK;
 }
 
@@ -869,19 +990,24 @@ extern "C" int nb_compute_gravity(nb_ctx* c) {
 }
 
 // n_sub velocity Verlet substeps (Physics.hpp:296-325) starting from Acceleration == a(x).
-static int verlet_substeps(nb_ctx* c, double h, long long n_sub, bool more_follow, bool pot) {
-    if (n_sub <= 0) return NB_OK;
+// Steady state is ONE launch per substep: the previous kick epilogue already drifted this substep into
+// the shadow positions and packed its j-stream (and, sharded, its all-gather is already in flight).
+static int verlet_substeps(nb_ctx* c, double h, long long n_sub, bool pot) {
     const long long n_local = c->hi - c->lo;
-    // the first drift of a call cannot ride in an epilogue: stand-alone kernel, new generation
-    if (n_local > 0) {
-        verlet_drift_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
-                                                                                               0.5 * h * h);
-        c->kernel_launches++;
-    }
-    c->packed_valid = false;
     for (long long k = 0; k < n_sub; ++k) {
-        const bool last = (k + 1 == n_sub) && !more_follow;
-        NB_TRY(force_pass(c, last ? kVerletKick : kVerletKickDrift, pot && (k + 1 == n_sub), h));
+        if (c->spec_valid && c->spec_h == h && c->packed_valid) {
+            commit_drift(c);
+        } else {
+            // first substep after an upload / edit / change of dt: stand-alone drift, new generation
+            c->drop_speculation();
+            if (n_local > 0) {
+                verlet_drift_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
+                                                                                                       0.5 * h * h);
+                c->kernel_launches++;
+            }
+            c->packed_valid = false; c->drop_speculation();
+        }
+        NB_TRY(force_pass(c, kVerletKickDrift, pot && (k + 1 == n_sub), h));
     }
     return NB_OK;
 }
@@ -915,11 +1041,11 @@ extern "C" int nb_integrate(nb_ctx* c, float dt) {
                                                                                                  c->cfg.max_speed);
             c->kernel_launches++;
         }
-        c->packed_valid = false;
+        c->packed_valid = false; c->drop_speculation();
         c->acc_valid = false;
         for (int k = 1; k < n_steps; ++k) NB_TRY(force_pass(c, kEuler, false, h));
     } else {
-        NB_TRY(verlet_substeps(c, h, n_steps, false, false));
+        NB_TRY(verlet_substeps(c, h, n_steps, false));
         c->acc_valid = true;  // Physics.hpp:324
     }
     NB_CUDA(cudaGetLastError());
@@ -949,7 +1075,7 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
         c->force_evals += total + first_force;
         c->interactions += (double)(total + first_force) * (double)c->n * (double)c->n;
         c->acc_valid = verlet;  // Euler: Acceleration holds a(x) of the positions before the last move
-        c->packed_valid = false;
+        c->packed_valid = false; c->drop_speculation();
         c->step_diag_exact = pot;
         return NB_OK;
     }
@@ -976,7 +1102,7 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
         // the gravity system's evaluation is only needed when Acceleration != a(x)
         if (!c->acc_valid) NB_TRY(force_pass(c, kForceOnly, false, 0.0));
         c->acc_valid = true;
-        NB_TRY(verlet_substeps(c, h, total, false, pot));
+        NB_TRY(verlet_substeps(c, h, total, pot));
     }
     return NB_OK;
 }
@@ -1061,8 +1187,9 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
         c->step_diag_valid = false;
         return finish_diag(c, rows, out);
     }
+    // hot loop B (Physics.hpp:148-161) through the potential-only instantiation of the force kernel, over a
+    // stream packed with this function's own rules (every body with a finite position, raw masses)
     NB_CUDA(cudaMemsetAsync(c->extent + kDiagExtentSlot, 0, sizeof(unsigned int), c->stream));
-    long long rows = 0;
     if (n_local > 0) {
         const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kDiagThreads), 4 * c->sm_count);
         diag_extent_kernel<<<grid, kDiagThreads, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->lo, c->hi, c->extent);
@@ -1073,26 +1200,27 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
         NB_NCCL(g_nccl.AllReduce(slot, slot, 1, kNcclUint32, kNcclMax, c->nccl_comm, c->stream));
     }
     if (n_local > 0) {
-        diag_pack_kernel<<<blocks_for(n_local, kDiagThreads), kDiagThreads, 0, c->stream>>>(
-            s.x[0], s.x[1], s.x[2], c->mass, c->lo, c->hi, c->extent, c->mass_exp, c->dpk);
+        const long long groups = (c->tiles_per_rank * kTileBodies) / kGroupBodies;
+        pack_kernel<true><<<(unsigned int)groups, kGroupBodies, 0, c->stream>>>(
+            s, c->order, c->dpk, c->dpk_lo, c->dhdr, nullptr, c->extent, kDiagExtentSlot, c->mass_exp, 1.0, 0.f);
         c->kernel_launches++;
     }
     if (c->world > 1) {
-        const size_t count = (size_t)c->tiles_per_rank * kTileBodies * 4;
-        float* buf = reinterpret_cast<float*>(c->dpk);
-        NB_NCCL(g_nccl.AllGather(buf + (size_t)c->rank * count, buf, count, kNcclFloat32, c->nccl_comm, c->stream));
+        const size_t rows_r = (size_t)c->tiles_per_rank * kTileBodies;
+        const size_t count = rows_r * 4;
+        const size_t hdr_count = rows_r / kGroupBodies * (sizeof(GroupHdr) / sizeof(float));
+        float* hdb = reinterpret_cast<float*>(c->dhdr);
+        NB_NCCL(g_nccl.GroupStart());
+        NB_NCCL(g_nccl.AllGather(c->dpk + (size_t)c->rank * count, c->dpk, count, kNcclFloat32, c->nccl_comm, c->stream));
+        NB_NCCL(g_nccl.AllGather(c->dpk_lo + (size_t)c->rank * count, c->dpk_lo, count, kNcclFloat32, c->nccl_comm,
+                                 c->stream));
+        NB_NCCL(g_nccl.AllGather(hdb + (size_t)c->rank * hdr_count, hdb, hdr_count, kNcclFloat32, c->nccl_comm, c->stream));
+        NB_NCCL(g_nccl.GroupEnd());
     }
-    if (n_local > 0) {
-        rows = blocks_for(n_local, kDiagThreads);
-        diag_potential_kernel<<<(unsigned int)rows, kDiagThreads, 0, c->stream>>>(
-            c->dpk, c->n, c->lo, c->hi, s.x[0], s.x[1], s.x[2], s.v[0], s.v[1], s.v[2], c->mass, c->extent, c->mass_exp,
-            c->cfg.g, c->cfg.softening, c->diag_part);
-        c->kernel_launches++;
-        c->interactions += (double)n_local * (double)c->n;
-    }
+    NB_TRY(launch_force(c, 0, kDiagOnly, 2, 0.0));
     NB_CUDA(cudaGetLastError());
     c->step_diag_valid = false;  // diag_part was overwritten
-    return finish_diag(c, rows, out);
+    return finish_diag(c, n_local > 0 ? c->step_diag_rows : 0, out);
 }
 
 extern "C" int nb_step_diagnostics(nb_ctx* c, nb_diag* out) {
@@ -1142,7 +1270,12 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
     }
     NB_CUDA(cudaGetLastError());
     c->step_diag_valid = false;
-    // velocities changed: the gather filter may change, positions did not -> the j-stream stays valid
+    // velocities changed: a prepared drift is void, and the gather filter (finite velocities, Physics.hpp:198-199)
+    // may now pass bodies it dropped (a pinned body's NaN velocity was just reset) -> re-pack and re-evaluate
+    // like the reference's next gravity system does
+    c->drop_speculation();
+    c->packed_valid = false;
+    c->acc_valid = false;
     return NB_OK;
 }
 
@@ -1183,6 +1316,8 @@ extern "C" int nb_timer_begin(nb_ctx* c) {
 extern "C" int nb_timer_end(nb_ctx* c, float* elapsed_ms) {
     if (!c || !elapsed_ms) return fail(NB_ERR_INVALID, "nb_timer_end: null");
     NB_CUDA(cudaSetDevice(c->device));
+    // the exchange a step leaves in flight on the communication stream belongs to the step
+    if (c->world > 1) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     NB_CUDA(cudaEventRecord(c->ev_timer1, c->stream));
     NB_CUDA(cudaEventSynchronize(c->ev_timer1));
     NB_CUDA(cudaStreamSynchronize(c->comm_stream));
@@ -1225,6 +1360,49 @@ extern "C" int nb_counters(nb_ctx* c, int64_t* kernel_launches, int64_t* force_e
     if (kernel_launches) *kernel_launches = c->kernel_launches;
     if (force_evals) *force_evals = c->force_evals;
     if (interactions) *interactions = c->interactions;
+    return NB_OK;
+}
+
+extern "C" int nb_near_stats(nb_ctx* c, int enable, int64_t* visits, int64_t* near_visits) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_near_stats: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->near_stats) {
+        unsigned long long h[2] = {0, 0};
+        NB_CUDA(cudaMemcpy(h, c->near_stats, sizeof(h), cudaMemcpyDeviceToHost));
+        if (visits) *visits = (int64_t)h[0];
+        if (near_visits) *near_visits = (int64_t)h[1];
+    } else {
+        if (visits) *visits = 0;
+        if (near_visits) *near_visits = 0;
+    }
+    if (enable && !c->near_stats) NB_CUDA(cudaMalloc(&c->near_stats, 2 * sizeof(unsigned long long)));
+    if (c->near_stats) NB_CUDA(cudaMemset(c->near_stats, 0, 2 * sizeof(unsigned long long)));
+    if (!enable && c->near_stats) {
+        cudaFree(c->near_stats);
+        c->near_stats = nullptr;
+    }
+    return NB_OK;
+}
+
+extern "C" int nb_overlap_profile(nb_ctx* c, int enable, float* ms4) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_overlap_profile: null context");
+    NB_CUDA(cudaSetDevice(c->device));
+    if (ms4) {
+        ms4[0] = ms4[1] = ms4[2] = ms4[3] = 0.f;
+        if (c->profile_comm && c->world > 1) {
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+            // the last Verlet step read generation `gen`: its own-sources launch (ev_own0/1) ran while the
+            // exchange of that generation (issued by the step before) was in flight on the communication stream
+            const int g = c->gen & 1;
+            NB_CUDA(cudaEventElapsedTime(&ms4[0], c->ev_own0, c->ev_own1));      // own-sources launch
+            NB_CUDA(cudaEventElapsedTime(&ms4[1], c->ev_own0, c->ev_comm0[g]));  // exchange start - launch start
+            NB_CUDA(cudaEventElapsedTime(&ms4[2], c->ev_own0, c->ev_comm1[g]));  // exchange end   - launch start
+            NB_CUDA(cudaEventElapsedTime(&ms4[3], c->ev_comm0[g], c->ev_comm1[g]));
+        }
+    }
+    c->profile_comm = enable != 0;
     return NB_OK;
 }
 

@@ -59,7 +59,7 @@ EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", 
            "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
-           "nb_profile_forces", "nb_profile_read", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
+           "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
 SOLVER_DIRECT, SOLVER_REFERENCE = 0, 1
@@ -124,6 +124,9 @@ def load_library(path=LIB_PATH):
     L.nb_profile_forces.argtypes = [C.c_void_p, C.c_int]
     L.nb_profile_read.argtypes = [C.c_void_p, C.POINTER(C.c_int64), _dp]
     L.nb_comm_unique_id.argtypes = [C.c_void_p]
+    if hasattr(L, "nb_near_stats"):  # absent from developer A/B builds of older sources (NB_LIB_PATH)
+        L.nb_overlap_profile.argtypes = [C.c_void_p, C.c_int, _fp]
+        L.nb_near_stats.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     _lib = L
     return L
 
@@ -263,7 +266,20 @@ class Physics:
 
     def upload_state(self, pos, vel, acc, mass, pinned=None):
         """upload() that also carries the caller's Acceleration components (asserted == a(x))."""
+        pos = np.ascontiguousarray(pos, np.float64)
+        vel = np.ascontiguousarray(vel, np.float64)
+        mass = np.ascontiguousarray(mass, np.float32)
+        if pos.ndim != 2 or pos.shape[1] not in (2, 3) or vel.shape != pos.shape or mass.shape != (pos.shape[0],):
+            raise NbodyError(1, "upload_state: pos/vel must be (n,2) or (n,3), mass (n,)")
         n, dim = pos.shape
+        if acc is not None:
+            acc = np.ascontiguousarray(acc, np.float64)
+            if acc.shape != pos.shape:
+                raise NbodyError(1, "upload_state: acc must have the shape of pos")
+        if pinned is not None:
+            pinned = np.ascontiguousarray(pinned, np.uint8)
+            if pinned.shape != (n,):
+                raise NbodyError(1, "upload_state: pinned must be (n,)")
         _check(self._L.nb_upload_state(self._h, n, dim, pos.ctypes.data_as(_dp), vel.ctypes.data_as(_dp),
                                        None if acc is None else acc.ctypes.data_as(_dp), mass.ctypes.data_as(_fp),
                                        None if pinned is None else pinned.ctypes.data_as(_bp)))
@@ -271,6 +287,11 @@ class Physics:
 
     def download_into(self, pos, vel, acc):
         """download() into caller-owned (n,dim) float64 arrays (e.g. pinned ones)."""
+        n = self.num_bodies()
+        for a in (pos, vel, acc):  # written in place: must already be what the C side expects
+            if a is not None and not (isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.c_contiguous
+                                      and a.flags.writeable and a.shape == (n, self.dim)):
+                raise NbodyError(1, f"download_into: arrays must be writable C-contiguous float64 of shape ({n}, {self.dim})")
         fn = self._L.nb_download if self.dim == 2 else self._L.nb_download3
         _check(fn(self._h, *[None if a is None else a.ctypes.data_as(_dp) for a in (pos, vel, acc)]))
 
@@ -393,6 +414,18 @@ class Physics:
         k, f, x = C.c_int64(), C.c_int64(), C.c_double()
         _check(self._L.nb_counters(self._h, C.byref(k), C.byref(f), C.byref(x)))
         return dict(kernel_launches=k.value, force_evals=f.value, interactions=x.value)
+
+    def overlap_profile(self, enable=True):
+        """{own_ms, comm_start_ms, comm_end_ms, comm_ms} of the last sharded Verlet step (nb_overlap_profile)."""
+        v = (C.c_float * 4)()
+        _check(self._L.nb_overlap_profile(self._h, int(enable), v))
+        return dict(own_launch_ms=v[0], exchange_start_ms=v[1], exchange_end_ms=v[2], exchange_ms=v[3])
+
+    def near_stats(self, enable=True):
+        """(warp x group visits, near-path visits) of the force launches since the last call."""
+        a, b = C.c_int64(), C.c_int64()
+        _check(self._L.nb_near_stats(self._h, int(enable), C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def profile_forces(self, enable=True):
         _check(self._L.nb_profile_forces(self._h, int(enable)))

@@ -15,19 +15,17 @@ def relerr(a, ref):
 def accuracy(n=4096):
     pos, vel, mass = sc.uniform_disk(n)
     ref = o.compute_gravity(pos, vel, mass)
-    for packed in (1, 0):
-        for r in (4, 2, 1):
-            os.environ["NB_FORCE_R"] = str(r); os.environ["NB_FORCE_PACKED"] = str(packed)
-            ph = pkg.Physics(0); ph.upload(pos, vel, mass); ph.compute_gravity(); _, _, acc = ph.download()
-            e = relerr(acc, ref)
-            print(f"C2 acc n={n} packed={packed} R={r}: max {e.max():.3e} p99.9 {np.quantile(e,0.999):.3e} med {np.median(e):.3e}", flush=True)
-            ph.close()
-    os.environ.pop("NB_FORCE_R"); os.environ.pop("NB_FORCE_PACKED")
+    for r in (4, 3, 2, 1):
+        os.environ["NB_FORCE_R"] = str(r)
+        ph = pkg.Physics(0); ph.set_precision(pkg.PRECISION_FP32); ph.upload(pos, vel, mass); ph.compute_gravity(); _, _, acc = ph.download()
+        e = relerr(acc, ref)
+        print(f"C2 acc n={n} R={r}: max {e.max():.3e} p99.9 {np.quantile(e,0.999):.3e} med {np.median(e):.3e}", flush=True)
+        ph.close()
+    os.environ.pop("NB_FORCE_R")
 
 def three_body():
     dt = pkg.dt_eff(np.float32(1.0)/np.float32(120), 1e6)
-    for packed in (2, 1, 0):
-        os.environ["NB_FORCE_PACKED"] = str(min(packed, 1))
+    for packed in (2, 1):
         for integ in (1, 0):
             ph = pkg.Physics(0); ph.set_config(integrator=integ)
             ph.set_precision(pkg.PRECISION_AUTO if packed == 2 else pkg.PRECISION_FP32)
@@ -44,15 +42,14 @@ def three_body():
                 p, v, a = ph.download()
                 print(f"C1 mode={["fp32-scalar","fp32-packed","exact"][packed]} integ={integ} steps={upto}: bitexact={np.array_equal(p,po) and np.array_equal(v,vo)} max|dx|/R {np.abs(p-po).max()/3.844e8:.3e} max|dE/E0| {emax:.3e} body0 {p[0]} P {d.momentum[:2]}", flush=True)
             ph.close()
-    os.environ.pop("NB_FORCE_PACKED")
 
 def timing(n, steps=3):
     pos, vel, mass = sc.plummer(n, dim=3)
     dt = 1e-3 * sc.crossing_time(n)
-    for packed in (1, 0):
-        for r in (4, 2, 1):
+    for packed in (1,):
+        for r in (4, 3, 2, 1):
             for nseg in (0,):
-                os.environ["NB_FORCE_R"] = str(r); os.environ["NB_FORCE_PACKED"] = str(packed); os.environ["NB_FORCE_NSEG"] = str(nseg)
+                os.environ["NB_FORCE_R"] = str(r); os.environ["NB_FORCE_NSEG"] = str(nseg)
                 ph = pkg.Physics(0); ph.upload(pos, vel, mass)
                 ph.step(dt, 1); ph.synchronize()
                 ph.timer_begin(); ph.step(dt, steps); ms = ph.timer_end()
