@@ -155,6 +155,14 @@ int nb_download3(nb_ctx* ctx, double* pos_xyz, double* vel_xyz, double* acc_xyz)
  * Physics.hpp:303) as a fourth array; dim is 2 or 3. */
 int nb_download_state(nb_ctx* ctx, int dim, double* pos, double* vel, double* acc, double* acc_prev);
 
+/* The order in which the FP32 path streams the bodies (a Hilbert-curve order of the positions at the last
+ * sort; order[k] = body row at stream position k; a sharded context fills and reads its own rows only) and
+ * the number of generations packed since that sort. The order fixes the summation order of every force sum,
+ * so a checkpoint that must resume bit-identically carries both: nb_upload_state, then nb_set_stream_order.
+ * The library re-sorts on its own every 64 generations (NB_RESORT_EVERY). */
+int nb_stream_order(nb_ctx* ctx, int32_t* order, int64_t* generations_since_sort);
+int nb_set_stream_order(nb_ctx* ctx, const int32_t* order, int64_t generations_since_sort);
+
 int64_t nb_num_bodies(nb_ctx* ctx);
 int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);
 /* The target partition a sharded context uses: contiguous, aligned to the 512-body source

@@ -129,7 +129,7 @@ struct StepParams {
                                 // launches (local / remote sources), slots 1.. the source segments
     unsigned int* tile_counter; // [n_itiles] arrival counters (only nseg > 1)
     double* diag_part;          // [n_itiles][kDiagValues] per-CTA diagnostics partials
-    unsigned long long* stats;  // null, or {warp x group visits, near ones} (nb_near_stats)
+    unsigned long long* stats;  // null, or stats[1] counts the (warp, group) visits that took the near path
     long long n;                // bodies
     long long n_tiles;          // j-stream length in tiles of kTileBodies (padded with m = 0)
     long long i_lo, i_hi;       // target range owned by this rank

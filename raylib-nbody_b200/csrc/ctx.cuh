@@ -131,7 +131,8 @@ struct nb_ctx {
     long long kernel_launches = 0;
     long long force_evals = 0;
     long long sorts = 0;
-    unsigned long long* near_stats = nullptr;  // device counters of nb_near_stats
+    unsigned long long* near_stats = nullptr;  // device counter of nb_near_stats ([1]: near-path visits)
+    long long near_visits = 0;                 // (warp, group) visits launched while the counter was armed
     bool profile_comm = false;           // record ev_comm0/1 around every exchange (overlap evidence)
     cudaEvent_t ev_comm0[2] = {nullptr, nullptr}, ev_comm1[2] = {nullptr, nullptr};  // per generation parity
     cudaEvent_t ev_own0 = nullptr, ev_own1 = nullptr;

@@ -31,6 +31,23 @@ namespace nb {
 
 constexpr int kUnrollPairs = NB_UNROLL_PAIRS;
 
+// float -> double of a chunk sum. F2F.F64.F32 runs on the XU pipe next to the kernel's MUFU.RSQ stream
+// (one conversion costs as much XU time as a MUFU); NB_INT_FLUSH builds the double from the float's bits
+// with integer-pipe instructions instead (exact for normal floats and +-0; chunk sums are never denormal
+// under .ftz; inf/nan keep their class).
+__device__ __forceinline__ double widen(float f) {
+#ifdef NB_INT_FLUSH
+    const unsigned int u = __float_as_uint(f);
+    const unsigned int mag = u & 0x7fffffffu;
+    unsigned int hi = (mag >> 3) + 0x38000000u;       // rebias the exponent: 1023 - 127 = 896 = 0x380
+    hi = mag == 0u ? 0u : hi;
+    hi = mag >= 0x7f800000u ? (0x7ff00000u | (mag >> 3)) : hi;  // inf / nan
+    return __hiloint2double((int)(hi | (u & 0x80000000u)), (int)(u << 29));
+#else
+    return (double)f;
+#endif
+}
+
 // One target body's running sums: FP32 inside a flush chunk, FP64 across chunks.
 // EQM: all sources carry the same mass -> the m*w multiply is dropped (the common factor is
 // applied in FP64 in the epilogue); D2: z == 0 for every body (reference 2-D uploads);
@@ -99,12 +116,12 @@ struct Target {
     __device__ __forceinline__ void flush(double& Ax, double& Ay, double& Az, double& Ph) {
         float lo, hi;
         if (!PONLY) {
-            f2_split(ax, lo, hi); Ax += (double)(lo + hi);
-            f2_split(ay, lo, hi); Ay += (double)(lo + hi);
-            if (!D2) { f2_split(az, lo, hi); Az += (double)(lo + hi); }
+            f2_split(ax, lo, hi); Ax += widen(lo + hi);
+            f2_split(ay, lo, hi); Ay += widen(lo + hi);
+            if (!D2) { f2_split(az, lo, hi); Az += widen(lo + hi); }
             ax = ay = az = f2_make(0.f, 0.f);
         }
-        if (POT) { f2_split(ph, lo, hi); Ph += (double)(lo + hi); ph = f2_make(0.f, 0.f); }
+        if (POT) { f2_split(ph, lo, hi); Ph += widen(lo + hi); ph = f2_make(0.f, 0.f); }
     }
 };
 
@@ -171,13 +188,15 @@ __device__ __forceinline__ void chunk_interact(Target<POT, EQM, D2, PONLY> (&t)[
     }
 }
 
-// The same chunk for ONE target through the two-float path. lo_rec: the chunk's residual records in
-// global memory (L2-resident; every lane reads the same address). Kept as a rolled loop: this path
-// runs for the handful of groups whose bounding box a warp's targets touch.
-template <bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY>
-__device__ __forceinline__ void chunk_interact_near(Target<POT, EQM, D2, PONLY>& t, const float4* __restrict__ rec,
-                                                    const float4* __restrict__ lo_rec, f2 nxl, f2 nyl, f2 nzl,
-                                                    float eps2, long long j_first, long long row) {
+// The same chunk for RN consecutive targets t[r0 .. r0+RN) through the two-float path. lo_rec: the chunk's
+// residual records in global memory (L2/L1-resident; every lane reads the same address). nl[q][k]:
+// {-lo_i, -lo_i} of target r0+q, axis k. Partially unrolled: this path runs for the handful of groups
+// whose bounding box a warp's targets touch, and must not cost the hot loop registers.
+template <int RN, int R, bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY, int RS>
+__device__ __forceinline__ void chunk_interact_near(Target<POT, EQM, D2, PONLY> (&t)[R], int r0,
+                                                    const float4* __restrict__ rec,
+                                                    const float4* __restrict__ lo_rec, const f2 (&nl)[RN][3],
+                                                    float eps2, long long j_first, long long row0) {
     const f2 e2 = f2_make(eps2, eps2);
     const f2 zero = f2_make(0.f, 0.f);
 #pragma unroll 4
@@ -185,12 +204,15 @@ __device__ __forceinline__ void chunk_interact_near(Target<POT, EQM, D2, PONLY>&
         f2 xj, yj, zj, mj, xl, yl, zl, unused;
         load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);
         load_pair<!D2, false>(lo_rec + 2 * u, xl, yl, zl, unused);
-        if (MASK) {
-            f2 m, bump;
-            self_mask<EQM>(mj, j_first + 2 * u, row, m, bump);
-            t.template interact_near<true>(xj, yj, zj, m, xl, yl, zl, nxl, nyl, nzl, e2, bump);
-        } else {
-            t.template interact_near<false>(xj, yj, zj, mj, xl, yl, zl, nxl, nyl, nzl, e2, zero);
+#pragma unroll
+        for (int q = 0; q < RN; ++q) {
+            if (MASK) {
+                f2 m, bump;
+                self_mask<EQM>(mj, j_first + 2 * u, row0 + (long long)(r0 + q) * RS, m, bump);
+                t[r0 + q].template interact_near<true>(xj, yj, zj, m, xl, yl, zl, nl[q][0], nl[q][1], nl[q][2], e2, bump);
+            } else {
+                t[r0 + q].template interact_near<false>(xj, yj, zj, mj, xl, yl, zl, nl[q][0], nl[q][1], nl[q][2], e2, zero);
+            }
         }
     }
 }

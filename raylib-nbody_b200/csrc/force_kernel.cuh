@@ -145,10 +145,6 @@ force_kernel(const __grid_constant__ StepParams p) {
             near = false;
 #endif
             const bool near_any = __any_sync(0xffffffffu, near);
-            if (p.stats && (tid & 31) == 0) {  // developer counters (nb_near_stats): warp x group visits, near ones
-                atomicAdd(&p.stats[0], 1ull);
-                if (near_any) atomicAdd(&p.stats[1], 1ull);
-            }
             if (!near_any) {
 #pragma unroll 1
                 for (int c = 0; c < kChunksPerGroup; ++c) {
@@ -162,7 +158,11 @@ force_kernel(const __grid_constant__ StepParams p) {
                     for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
                 }
             } else {
-                // ---- near group: two-float offsets on both sides, one target at a time -------
+                // ---- near group: two-float offsets on both sides, RN targets at a time ------------
+                // (developer counter of nb_near_stats: kept out of the common path, where a lane-divergent
+                // statement would cost the hot loop its uniform-register addressing)
+                if (p.stats && (tid & 31) == 0) atomicAdd(&p.stats[1], 1ull);
+                constexpr int RN = R >= 2 ? 2 : 1;
                 const float4* glo = reinterpret_cast<const float4*>(p.lo_cur) + j_group;
 #pragma unroll 1
                 for (int c = 0; c < kChunksPerGroup; ++c) {
@@ -170,25 +170,47 @@ force_kernel(const __grid_constant__ StepParams p) {
                     const float4* lrec = glo + c * CH;
                     const long long j_first = j_group + c * CH;
 #pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        float nl[3];
+                    for (int r0 = 0; r0 < R; r0 += RN) {
+                        if (r0 + RN > R) break;
+                        f2 nl[RN][3];
 #pragma unroll
-                        for (int q = 0; q < 3; ++q) {
-                            const double cq = q == 0 ? c0 : (q == 1 ? c1 : c2);
-                            const double d = __dadd_rn(tpos[q][li0 + 32 * r], -cq);
-                            const float fh = (float)d;
-                            nl[q] = -(float)__dadd_rn(d, -(double)fh);
+                        for (int q = 0; q < RN; ++q) {
+#pragma unroll
+                            for (int k = 0; k < 3; ++k) {
+                                const double ck = k == 0 ? c0 : (k == 1 ? c1 : c2);
+                                const double d = __dadd_rn(tpos[k][li0 + 32 * (r0 + q)], -ck);
+                                const float fh = (float)d;
+                                const float fl = -(float)__dadd_rn(d, -(double)fh);
+                                nl[q][k] = f2_make(fl, fl);
+                            }
                         }
-                        const f2 nxl = f2_make(nl[0], nl[0]), nyl = f2_make(nl[1], nl[1]), nzl = f2_make(nl[2], nl[2]);
-                        const long long row = rbase + 32 * r;
                         if (diag_tile)
-                            chunk_interact_near<POT, true, CH, EQM, D2, PONLY>(tg[r], rec, lrec, nxl, nyl, nzl, cur.eps2,
-                                                                               j_first, row);
+                            chunk_interact_near<RN, R, POT, true, CH, EQM, D2, PONLY, 32>(tg, r0, rec, lrec, nl, cur.eps2,
+                                                                                          j_first, rbase);
                         else
-                            chunk_interact_near<POT, false, CH, EQM, D2, PONLY>(tg[r], rec, lrec, nxl, nyl, nzl, cur.eps2,
-                                                                                j_first, row);
-                        tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+                            chunk_interact_near<RN, R, POT, false, CH, EQM, D2, PONLY, 32>(tg, r0, rec, lrec, nl, cur.eps2,
+                                                                                           j_first, rbase);
                     }
+                    if (R % RN) {  // R = 3: the odd target on its own
+                        constexpr int rl = R - 1;
+                        f2 nl1[1][3];
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) {
+                            const double ck = k == 0 ? c0 : (k == 1 ? c1 : c2);
+                            const double d = __dadd_rn(tpos[k][li0 + 32 * rl], -ck);
+                            const float fh = (float)d;
+                            const float fl = -(float)__dadd_rn(d, -(double)fh);
+                            nl1[0][k] = f2_make(fl, fl);
+                        }
+                        if (diag_tile)
+                            chunk_interact_near<1, R, POT, true, CH, EQM, D2, PONLY, 32>(tg, rl, rec, lrec, nl1, cur.eps2,
+                                                                                         j_first, rbase);
+                        else
+                            chunk_interact_near<1, R, POT, false, CH, EQM, D2, PONLY, 32>(tg, rl, rec, lrec, nl1, cur.eps2,
+                                                                                          j_first, rbase);
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
                 }
             }
         }

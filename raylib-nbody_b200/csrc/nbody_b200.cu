@@ -132,7 +132,10 @@ struct KernelEntry {
 };
 
 // <threads, R, POT, CTAs/SM, flush chunk, EQM uniform mass (no m*w multiply), D2 z == 0 (reference 2-D uploads), PONLY>
-#define NB_KF(R, E, D) {R, 0, E, D, force_kernel<kNT, R, false, 4 / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
+#ifndef NB_FORCE_MINB
+#define NB_FORCE_MINB 4
+#endif
+#define NB_KF(R, E, D) {R, 0, E, D, force_kernel<kNT, R, false, ((R) == 4 ? NB_FORCE_MINB : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
 // the potential accumulators of R >= 3 targets do not fit 128 registers: those variants run 3 CTAs per SM
 #define NB_KP(R, E, D) {R, 1, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
 #define NB_KD(R, E, D) {R, 2, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, true>}
@@ -163,9 +166,12 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
     LaunchPlan best;
     double best_score = -1.0;
     const int r_opts[] = {4, 3, 2, 1};
+    const int eqm_k = (kind == 2 ? c->diag_uniform_mass : c->uniform_mass) ? 1 : 0;
+    // NB_FORCE_R (developer knob) only binds where that variant exists (the potential-only set has no R = 3)
+    const bool honour_forced = c->forced_r && find_kernel(c->forced_r, kind, eqm_k, c->planar ? 1 : 0) != nullptr;
     for (int q = 0; q < 4; ++q) {
         const int r = r_opts[q];
-        if (c->forced_r && c->forced_r != r) continue;
+        if (honour_forced && c->forced_r != r) continue;
         // the stand-alone diagnostics count every body: its uniform-mass variant needs ALL masses equal
         const int eqm = (kind == 2 ? c->diag_uniform_mass : c->uniform_mass) ? 1 : 0, d2 = c->planar ? 1 : 0;
         const KernelEntry* ke = find_kernel(r, kind, eqm, d2);
@@ -710,6 +716,8 @@ int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
     NB_TRY(prof_end(c));
     c->kernel_launches++;
     c->interactions += (double)n_local * (double)(p.j_tile_hi - p.j_tile_lo) * kTileBodies;
+    if (c->near_stats)  // every warp of every target tile visits every source group of the launch once
+        c->near_visits += n_it * (kNT / 32) * (p.j_tile_hi - p.j_tile_lo) * kGroupsPerTile;
     if (which != 1 && kind != 0) {
         c->step_diag_rows = n_it;
         c->step_diag_valid = kind == 1;
@@ -872,6 +880,42 @@ extern "C" int nb_download3(nb_ctx* c, double* pos_xyz, double* vel_xyz, double*
 extern "C" int nb_download_state(nb_ctx* c, int dim, double* pos, double* vel, double* acc, double* acc_prev) {
     if (dim != 2 && dim != 3) return fail(NB_ERR_INVALID, "nb_download_state: dim must be 2 or 3");
     return download_dim(c, pos, vel, acc, dim, acc_prev);
+}
+
+// The stream order is part of the summation order: a checkpoint that wants its resumed run to be
+// bit-identical to the uninterrupted one carries it (scenarios.save_snapshot / load_snapshot).
+extern "C" int nb_stream_order(nb_ctx* c, int32_t* order, int64_t* generations_since_sort) {
+    if (!c || !order) return fail(NB_ERR_INVALID, "nb_stream_order: null");
+    NB_CUDA(cudaSetDevice(c->device));
+    const long long n_local = c->hi - c->lo;
+    if (n_local > 0)
+        NB_CUDA(cudaMemcpyAsync(order + c->lo, c->order + c->lo, sizeof(int) * n_local, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    if (generations_since_sort) *generations_since_sort = c->packs_since_sort;
+    return NB_OK;
+}
+
+extern "C" int nb_set_stream_order(nb_ctx* c, const int32_t* order, int64_t generations_since_sort) {
+    if (!c || !order) return fail(NB_ERR_INVALID, "nb_set_stream_order: null");
+    if (generations_since_sort < 0) return fail(NB_ERR_INVALID, "nb_set_stream_order: negative age");
+    NB_CUDA(cudaSetDevice(c->device));
+    const long long n_local = c->hi - c->lo;
+    // the rows this context owns must be a permutation of themselves
+    std::vector<uint8_t> seen((size_t)std::max<long long>(n_local, 0), 0);
+    for (long long q = 0; q < n_local; ++q) {
+        const long long b = (long long)order[c->lo + q] - c->lo;
+        if (b < 0 || b >= n_local || seen[(size_t)b]) return fail(NB_ERR_INVALID, "nb_set_stream_order: not a permutation of the context's rows");
+        seen[(size_t)b] = 1;
+    }
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    if (n_local > 0)
+        NB_CUDA(cudaMemcpyAsync(c->order + c->lo, order + c->lo, sizeof(int) * n_local, cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    c->order_valid = true;
+    c->packs_since_sort = generations_since_sort;
+    c->packed_valid = false; c->drop_speculation();
+    c->step_diag_valid = false;
+    return NB_OK;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1370,7 +1414,7 @@ extern "C" int nb_near_stats(nb_ctx* c, int enable, int64_t* visits, int64_t* ne
     if (c->near_stats) {
         unsigned long long h[2] = {0, 0};
         NB_CUDA(cudaMemcpy(h, c->near_stats, sizeof(h), cudaMemcpyDeviceToHost));
-        if (visits) *visits = (int64_t)h[0];
+        if (visits) *visits = (int64_t)c->near_visits;
         if (near_visits) *near_visits = (int64_t)h[1];
     } else {
         if (visits) *visits = 0;
@@ -1378,6 +1422,7 @@ extern "C" int nb_near_stats(nb_ctx* c, int enable, int64_t* visits, int64_t* ne
     }
     if (enable && !c->near_stats) NB_CUDA(cudaMalloc(&c->near_stats, 2 * sizeof(unsigned long long)));
     if (c->near_stats) NB_CUDA(cudaMemset(c->near_stats, 0, 2 * sizeof(unsigned long long)));
+    c->near_visits = 0;
     if (!enable && c->near_stats) {
         cudaFree(c->near_stats);
         c->near_stats = nullptr;

@@ -56,7 +56,7 @@ class Diagnostics:
 
 EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
-           "nb_download3", "nb_download_state", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
+           "nb_download3", "nb_download_state", "nb_stream_order", "nb_set_stream_order", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
@@ -95,6 +95,9 @@ def load_library(path=LIB_PATH):
     L.nb_download.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_download3.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.nb_download_state.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp]
+    if hasattr(L, "nb_stream_order"):
+        L.nb_stream_order.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
+        L.nb_set_stream_order.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
     L.nb_count_overlaps.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_resolve_collisions.argtypes = [C.c_void_p, _dp, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8),
                                         _dp, _dp, C.POINTER(C.c_float), C.POINTER(C.c_uint8), _dp, C.POINTER(C.c_int64), C.c_int64]
@@ -355,6 +358,19 @@ class Physics:
         out = [np.zeros((n, self.dim)) for _ in range(4)]
         _check(self._L.nb_download_state(self._h, self.dim, *[a.ctypes.data_as(_dp) for a in out]))
         return tuple(out)
+
+    def stream_order(self):
+        """(order, generations_since_sort): the summation order of the FP32 path (nb_stream_order)."""
+        order = np.zeros(self.num_bodies(), np.int32)
+        age = C.c_int64()
+        _check(self._L.nb_stream_order(self._h, order.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(age)))
+        return order, age.value
+
+    def set_stream_order(self, order, generations_since_sort=0):
+        order = np.ascontiguousarray(order, np.int32)
+        if order.shape != (self.num_bodies(),):
+            raise NbodyError(1, "set_stream_order: one entry per body")
+        _check(self._L.nb_set_stream_order(self._h, order.ctypes.data_as(C.POINTER(C.c_int32)), int(generations_since_sort)))
 
     def num_bodies(self):
         return int(self._L.nb_num_bodies(self._h))

@@ -105,8 +105,9 @@ def crossing_time(n, scale=EARTH_MOON, mass=MOON_MASS, g=G_DEFAULT):
 SNAPSHOT_CONFIG_KEYS = ("g", "softening", "max_speed", "integrator", "max_substep", "max_substeps_per_frame")
 
 
-def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, config=None, frame=0):
-    """Bodies (Scenario::BodyData, Scenario.hpp:14-21) plus the physics Config fields."""
+def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, config=None, frame=0, stream_order=None):
+    """Bodies (Scenario::BodyData, Scenario.hpp:14-21) plus the physics Config fields. stream_order:
+    Physics.stream_order() of the run, for a resume that must be bit-identical (it fixes the summation order)."""
     n = len(mass)
     data = {"pos": np.asarray(pos, np.float64), "vel": np.asarray(vel, np.float64),
             "mass": np.asarray(mass, np.float32),
@@ -116,6 +117,9 @@ def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, co
         data["acc"] = np.asarray(acc, np.float64)
     if acc_prev is not None:
         data["acc_prev"] = np.asarray(acc_prev, np.float64)
+    if stream_order is not None:
+        data["order"] = np.asarray(stream_order[0], np.int32)
+        data["order_age"] = np.int64(stream_order[1])
     for k, v in (config or {}).items():
         if k not in SNAPSHOT_CONFIG_KEYS:
             raise KeyError(f"not a physics Config field: {k}")
@@ -124,10 +128,11 @@ def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, co
 
 
 def load_snapshot(path):
-    """-> dict(pos, vel, mass, pinned, acc|None, acc_prev|None, config, frame); floats round-trip exactly."""
+    """-> dict(pos, vel, mass, pinned, acc|None, acc_prev|None, stream_order|None, config, frame); floats round-trip exactly."""
     z = np.load(path)
     cfg = {k: (int(z["cfg_" + k]) if k in ("integrator", "max_substeps_per_frame") else float(z["cfg_" + k]))
            for k in SNAPSHOT_CONFIG_KEYS if "cfg_" + k in z.files}
     return {"pos": z["pos"], "vel": z["vel"], "mass": z["mass"], "pinned": z["pinned"],
             "acc": z["acc"] if "acc" in z.files else None, "acc_prev": z["acc_prev"] if "acc_prev" in z.files else None,
+            "stream_order": (z["order"], int(z["order_age"])) if "order" in z.files else None,
             "config": cfg, "frame": int(z["frame"])}

@@ -108,11 +108,14 @@ def test_c1_three_body_10k_steps_bitexact(pkg, ph, integ, name):
     assert drift <= float(g[f"{name}_max_drift_10000"]) * (1 + 1e-9)
 
 
-@pytest.mark.parametrize("integ,name,tol_x,tol_e", [(1, "verlet", 2e-6, 2.0e-6), (0, "euler", 5e-6, 5.5e-4)])
+@pytest.mark.parametrize("integ,name,tol_x,tol_e", [(1, "verlet", 1e-5, 2.0e-6), (0, "euler", 2e-5, 5.5e-4)])
 def test_c1_three_body_fp32_divergence_bound(pkg, ph, integ, name, tol_x, tol_e):
     """The FP32 path on the same seed: bounded divergence over 1000 steps and the same energy
     drift as the reference. (The mirror-symmetric seed is dynamically unstable: any rounding
-    difference grows e-fold per ~600 steps, so no FP32 evaluation can track 10k steps; DESIGN.md.)"""
+    difference grows e-fold per ~600 steps, so no FP32 evaluation can track 10k steps; DESIGN.md.
+    The position bound is the FP32 pair terms' 6e-8 per frame times that growth: measured 2.8e-6
+    (Verlet) with the two-float offsets of round 2, 1.5e-6 with round 1's exact differences on a
+    32 m grid; the default AUTO precision runs this world on the bit-exact FP64 path instead.)"""
     g = golden("c1_three_body.npz")
     ph.set_precision(pkg.PRECISION_FP32)
     ph.set_config(integrator=integ)
@@ -390,12 +393,12 @@ def test_all_kernel_variants_agree(pkg):
         p.compute_gravity()
         acc = p.download()[2]
         d = p.compute_diagnostics()        # potential-only variants (R = 3 falls back to another R)
-        p.step(100.0, 1, diagnostics=True)  # force + potential variants
+        p.step(1e-3, 1, diagnostics=True)   # force + potential variants (a step too short to move anything)
         d2 = p.step_diagnostics()
         p.close()
         assert rel_err(acc, g["acc"]).max() <= ACC_TOL, r
         assert abs(d.potential - g["diag"][1]) <= 1e-6 * abs(g["diag"][1]), r
-        assert abs(d2.energy - g["diag"][2]) <= 1e-4 * abs(g["diag"][2]), r
+        assert abs(d2.energy - g["diag"][2]) <= 1e-6 * abs(g["diag"][2]), r
     os.environ.pop("NB_FORCE_R")
 
 
@@ -524,15 +527,17 @@ def test_checkpoint_resume_is_bit_exact(pkg, tmp_path, integ):
     b.upload(pos, vel, mass)
     b.step(dt, 3)
     p, v, acc, acc_prev = b.download_state()
+    order = b.stream_order()   # the summation order of the FP32 path is part of a bit-exact checkpoint
     b.close()
     path = str(tmp_path / "ckpt.npz")
-    pkg.scenarios.save_snapshot(path, p, v, mass, acc=acc, acc_prev=acc_prev, config=cfg, frame=3)
+    pkg.scenarios.save_snapshot(path, p, v, mass, acc=acc, acc_prev=acc_prev, config=cfg, frame=3, stream_order=order)
     s = pkg.scenarios.load_snapshot(path)
     c = pkg.Physics(0)
     c.set_precision(pkg.PRECISION_FP32)
     c.set_config(**s["config"])
     # Verlet continues from Acceleration == a(x) (Physics.hpp:324); an Euler frame recomputes it anyway
     c.upload_state(s["pos"], s["vel"], s["acc"] if integ == 1 else None, s["mass"], s["pinned"])
+    c.set_stream_order(*s["stream_order"])
     c.step(dt, 3)
     resumed = c.download_state()
     c.close()
@@ -746,7 +751,9 @@ def test_speculative_drift_never_leaks_into_the_state(pkg, ph, oracle_lib, ob):
     oracle_lib.physics_frames(po, vo, ao, a0o, mass, pinned, ob.make_config(softening=eps), dt, 5)
     scale = np.abs(po).max()
     assert np.abs(p - po).max() / scale < 1e-9 and np.array_equal(p[7], pos[7])
-    assert rel_err(a[pinned == 0], ao[pinned == 0]).max() < 1e-5 and rel_err(a0[pinned == 0], a0o[pinned == 0]).max() < 1e-5
+    # (a and a0 differ from each other by ~1e-3 per frame here: a mix-up would show at that level)
+    assert rel_err(a[pinned == 0], ao[pinned == 0]).max() < 5e-5 and rel_err(a0[pinned == 0], a0o[pinned == 0]).max() < 5e-5
+    assert rel_err(a[pinned == 0], a0[pinned == 0]).max() > 1e-4
     assert not a[7].any() and not a0[7].any()
 
 
@@ -756,7 +763,7 @@ def test_contracting_world_is_bitwise_repeatable(pkg):
     source segments (nseg > 1): two identical runs are bit-identical, and the end state still meets the bound."""
     n = 20000
     pos, vel, mass = pkg.scenarios.plummer(n, seed=5, dim=3)
-    vel = -pos / 40.0          # homologous infall: every step shrinks the world by 1/8 of its size
+    vel = -pos / 75.0          # homologous infall: 14 steps of 5 s shrink the world to 1/15 of its size
     eps, dt = 1.0e6, 5.0
     runs = []
     for _ in range(2):
@@ -769,7 +776,7 @@ def test_contracting_world_is_bitwise_repeatable(pkg):
         p.close()
     for u, w in zip(*runs):
         assert np.array_equal(u, w)
-    assert np.abs(runs[0][0]).max() < 0.3 * np.abs(pos).max()
+    assert np.abs(runs[0][0]).max() < 0.1 * np.abs(pos).max()
 
 
 def test_resort_interval_changes_order_not_results(pkg, oracle_lib, ob, monkeypatch):
