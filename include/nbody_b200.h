@@ -102,6 +102,17 @@ typedef struct nb_diag {
 /* One context on CUDA device `device`. */
 int nb_create(int device, nb_ctx** out);
 
+/* A single-process context over n_dev GPUs of one box (1 <= n_dev <= 8; every pair must have peer access:
+ * NVLink/NVSwitch). The reference is one process with one thread (src/main.cpp:100-143), so this — not
+ * nb_create_sharded — is what its flecs systems can hold: the targets are partitioned over the devices like
+ * nb_partition(n, i, n_dev), every call on the returned handle drives all devices, uploads and downloads use
+ * the caller's full arrays, and the per-step exchange of packed positions is done by the packing kernels'
+ * own stores into the peers' memory (no NCCL). n_dev == 1 is nb_create. Same restrictions as a sharded
+ * context: FP32 path only (no FP64_EXACT, no NB_SOLVER_REFERENCE, no collision pass). */
+int nb_create_multi(const int* devices, int n_dev, nb_ctx** out);
+/* Devices behind a handle (1 for nb_create / nb_create_sharded contexts). */
+int nb_num_devices(nb_ctx* ctx);
+
 /* Target-partitioned context: rank `rank` of `world` owns bodies [lo,hi) of every upload
  * (nb_local_range) and exchanges packed positions with its peers through NCCL once per
  * force evaluation. `nccl_unique_id` is the 128-byte id from nb_comm_unique_id() on rank 0,
@@ -234,6 +245,9 @@ int nb_count_overlaps(nb_ctx* ctx, const double* radius, int64_t* n_overlaps, in
 int nb_resolve_collisions(nb_ctx* ctx, const double* radius, const double* density, int64_t* n_merges,
                           uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
                           uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap);
+
+/* Test hook: the device restatement of glibc's cbrt (update_radius_from_mass, Collision.hpp:37-46) on n values. */
+int nb_debug_cbrt(nb_ctx* ctx, const double* in, double* out, int64_t n);
 
 /* Substep plan of Physics.hpp:268-271 (float arithmetic). Host-only helper. */
 int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub);

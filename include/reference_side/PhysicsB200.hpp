@@ -71,6 +71,7 @@ public:
         int solver = NB_SOLVER_DIRECT;
         int applied_solver = -1, applied_bh_threshold = 0;
         float applied_bh_theta = 0.0f;
+        int n_devices = 1;
         long long uploads = 0, frames = 0;
         long long collision_checks = 0, collision_frames = 0, merges = 0;  // device passes / frames with a merge / merges
         // Verlet: the kick pass of frame k also accumulates the potential at the positions frame k+1 starts
@@ -243,6 +244,15 @@ public:
         Bodies b = sync(w, d);
         const size_t n = b.size();
         if (n < 2) return;  // Collision.hpp:70
+        if (d.n_devices > 1) {
+            // the collision pass is a single-GPU operation: a multi-GPU world must not need it
+            bool any = false;
+            w.each([&](const flecs::entity e, const Position&, const Mass& m) {
+                any = any || nbody::systems::Collision::radius_of(e, m) > 0.0;
+            });
+            if (any) throw std::runtime_error("PhysicsB200: a multi-GPU context has no collision pass; give bodies Radius{0}");
+            return;
+        }
         std::vector<flecs::entity> ents;
         std::vector<double> radius, density;
         ents.reserve(n); radius.reserve(n); density.reserve(n);
@@ -296,9 +306,18 @@ public:
     // what the gravity system followed by integrate() computes. Trails (system 4) stay with the
     // reference's renderer.
     static void register_systems(const flecs::world& w, int device = 0, int solver = NB_SOLVER_DIRECT) {
+        register_systems(w, std::vector<int>{device}, solver);
+    }
+
+    // Several GPUs behind the same single-threaded flecs systems (the reference is one process, main.cpp:100-143):
+    // nb_create_multi partitions the targets over `devices` and exchanges packed positions through peer memory.
+    // Multi-GPU contexts run the all-pairs path only: no collision pass (bodies must carry Radius{0}) and the
+    // direct solver.
+    static void register_systems(const flecs::world& w, const std::vector<int>& devices, int solver = NB_SOLVER_DIRECT) {
         Device d;
         d.solver = solver;
-        check(nb_create(device, &d.ctx), "nb_create");
+        check(nb_create_multi(devices.data(), (int)devices.size(), &d.ctx), "nb_create_multi");
+        d.n_devices = nb_num_devices(d.ctx);
         w.set<Device>(d);
 
         w.system<>().kind(flecs::OnUpdate).iter([&](flecs::iter&) {

@@ -175,6 +175,13 @@ class Oracle:
             return int(k), alive, changed, p, v, m, pin, r, log[:int(k)]
         return int(k), alive, changed, p, v, m, pin, r
 
+    def cbrt(self, x):
+        """libm's cbrt (what std::cbrt is in the reference's build), element-wise."""
+        x = np.ascontiguousarray(x, np.float64)
+        out = np.zeros_like(x)
+        self.lib.orc_cbrt(C.c_int64(x.size), _d(x), _d(out))
+        return out
+
     def zero_net_momentum(self, vel, mass, pinned=None):
         n = vel.shape[0]
         self.lib.orc_zero_net_momentum(C.c_int64(n), _d(vel), _f(mass), _b(pinned))

@@ -111,6 +111,8 @@ void expect(bool ok, const char* what) {
 }  // namespace
 
 int main() {
+    const char* only = std::getenv("NB_DROPIN_ONLY");  // "F": just the multi-GPU scenario
+    if (!(only && only[0] == 'F')) {
     // ---- A: config 1, the built-in three-body seed; n <= 512 runs the FP64 exact path ----------
     for (int integrator : {1, 0}) {
         flecs::world wr, wb;
@@ -356,6 +358,62 @@ int main() {
                     "diagnostics): reference %.3f s, binding %.6f s  (x%.0f)\n", tr, tb, tr / tb);
         expect(tb < tr, "the binding's default-settings frame is faster than the reference's");
         PhysicsB200::shutdown(wb);
+    }
+    }  // scenarios A-E
+    // ---- F: several GPUs behind the same flecs systems (nb_create_multi); devices from NB_DROPIN_DEVICES="0,1,.." -
+    if (const char* list = std::getenv("NB_DROPIN_DEVICES")) {
+        std::vector<int> devices;
+        for (const char* q = list; *q;) {
+            devices.push_back(std::atoi(q));
+            while (*q && *q != ',') ++q;
+            if (*q == ',') ++q;
+        }
+        {
+            flecs::world wr, wb;
+            make_config(wr, 1);
+            make_config(wb, 1);
+            Physics::register_systems(wr);
+            PhysicsB200::register_systems(wb, devices);
+            add_disk(wr, 16384, 5, 4.0f);   // the reference's default softening
+            add_disk(wb, 16384, 5, 4.0f);
+            for (flecs::world* w : {&wr, &wb}) w->get_mut<Config>()->time_scale = 3.0e4f;  // dtEff = 250 s
+            const float dt = wr.get<Config>()->fixed_dt;
+            for (int f = 0; f < 3; ++f) {
+                wr.progress(dt);
+                wb.progress(dt);
+            }
+            const Snapshot r = snap(wr), b = snap(wb);
+            std::printf("16384-body disk on %zu GPUs in one process, softening 4 m, Verlet x3\n", devices.size());
+            const double ep = max_rel(b.pos, r.pos), ev = max_rel(b.vel, r.vel), ea = max_rel(b.acc, r.acc);
+            std::printf("  max |dpos|/max|pos| %.3e  max |dvel|/max|vel| %.3e  max |dacc|/max|acc| %.3e\n", ep, ev, ea);
+            expect(ep < 1e-9 && ev < 1e-6 && ea < 1e-5, "multi-GPU trajectories within the FP32-path bounds");
+            const auto* dr = wr.get<Physics::Diagnostics>();
+            const auto* db = wb.get<Physics::Diagnostics>();
+            expect(dr && db && dr->ok && db->ok && std::fabs(dr->energy - db->energy) <= 2e-6 * std::fabs(dr->energy),
+                   "Diagnostics energy within 2e-6");
+            expect(wb.get<PhysicsB200::Device>()->uploads == 1, "state stayed device-resident (one upload)");
+            PhysicsB200::shutdown(wb);
+        }
+        // whole-frame time of the binding at 2^17 bodies: one GPU beside all of them (no reference twin: one of its
+        // frames takes minutes at this size)
+        double t_one = 0.0, t_all = 0.0;
+        for (int pass = 0; pass < 2; ++pass) {
+            flecs::world wb;
+            make_config(wb, 1);
+            if (pass == 0) PhysicsB200::register_systems(wb, std::vector<int>{devices[0]});
+            else PhysicsB200::register_systems(wb, devices);
+            add_disk(wb, 131072, 6, 1.0e6f);
+            wb.get_mut<Config>()->time_scale = 3.0e4f;
+            const float dt = wb.get<Config>()->fixed_dt;
+            for (int f = 0; f < 3; ++f) wb.progress(dt);
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int f = 0; f < 10; ++f) wb.progress(dt);
+            const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() / 10;
+            (pass == 0 ? t_one : t_all) = sec;
+            PhysicsB200::shutdown(wb);
+        }
+        std::printf("131072-body frame through the binding (gather, step + diagnostics, scatter): 1 GPU %.4f s, %zu GPUs %.4f s\n",
+                    t_one, devices.size(), t_all);
     }
     std::printf(failures ? "DROPIN CHECK FAILED (%d)\n" : "DROPIN CHECK PASSED\n", failures);
     return failures ? 1 : 0;

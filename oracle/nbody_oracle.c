@@ -429,3 +429,9 @@ void orc_radius_from_mass(int64_t n, const float* mass, const double* density, d
         radius[i] = cbrt((3.0 * safe) / (4.0 * pi * density[i]));
     }
 }
+
+/* libm's cbrt on an array: the reference's update_radius_from_mass (Collision.hpp:37-46) calls std::cbrt, so
+ * the device restatement of it (csrc/merge.cuh::cbrt_glibc) is pinned against this machine's libm. */
+void orc_cbrt(int64_t n, const double* in, double* out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = cbrt(in[i]);
+}

@@ -8,9 +8,8 @@
 // common frame, and an O(N^2) FP64 loop on one host core (22 ms at N = 4096, ~25 min at 2^20). The
 // kernels here evaluate exactly that predicate, in the reference's operation order with
 // non-contracted FP64 arithmetic: over all pairs (count, first pair, optionally the list of pairs:
-// nb_count_overlaps and the first step of nb_resolve_collisions), and for one changed body against
-// all others (the rescan after every merge of nb_resolve_collisions, which replays the merges in the
-// reference's order on the host; see the comment above that function in nbody_b200.cu).
+// nb_count_overlaps and the first step of nb_resolve_collisions); the merges themselves are replayed
+// in the reference's order by merge_replay_kernel (merge.cuh), which re-tests pairs with this predicate.
 //
 // FP64-pipe bound: 8 FP64 operations per pair; triangular sweep (j-tiles at or after the
 // target's own tile).
@@ -249,48 +248,6 @@ __global__ void __launch_bounds__(256) grid_overlap_kernel(const double* __restr
         atomicAdd(&result[0], count);
         atomicMin(&result[1], first);
     }
-}
-
-// ---- merge phase support (nb_resolve_collisions) --------------------------------------------------
-// The merges themselves are sequential (Collision.hpp:75-132: the survivor's position, mass and radius
-// change between pair tests) and are replayed on the host in the reference's order; the device keeps a
-// scratch copy of the CURRENT positions/radii/alive flags and answers, after every merge, "which living
-// bodies does the survivor's new state overlap?" — the only pairs whose outcome the merge can change.
-
-// One launch per merge: record the merge in the scratch state (survivor s moved/grew, body d died; d < 0: nobody
-// newly died) and report every living k != s whose current state overlaps the survivor's new one.
-// out[0] is a running total of hits over the whole replay (base = its value before this launch), the hits of
-// this launch land in out[1 + (slot - base)]: no counter reset, no second launch, one readback.
-__global__ void __launch_bounds__(256) collide_rescan_kernel(double* cx, double* cy, double* cr, unsigned char* live,
-                                                             long long n, long long s, double sx, double sy, double sr,
-                                                             long long d, unsigned int* out, unsigned int base) {
-    const long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    if (k == s) {  // every other thread reads its own row only
-        cx[s] = sx; cy[s] = sy; cr[s] = sr;
-        return;
-    }
-    if (k == d) {
-        live[d] = 0;
-        return;
-    }
-    if (!live[k]) return;
-    // (x_B - x_A)^2 and r_A + r_B do not depend on which of the two is A: one form serves both orders
-    const double dx = __dsub_rn(cx[k], sx);
-    const double dy = __dsub_rn(cy[k], sy);
-    const double rsum = __dadd_rn(sr, cr[k]);
-    const double dist2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-    if (!(dist2 > __dmul_rn(rsum, rsum))) out[1 + (atomicAdd(&out[0], 1u) - base)] = (unsigned int)k;
-}
-
-// scratch copies for the merge phase: positions, radii (already on the device), live = passes the input filter
-__global__ void __launch_bounds__(256) collide_snapshot_kernel(const double* __restrict__ x0, const double* __restrict__ x1,
-                                                               const double* __restrict__ x2, const float* __restrict__ mass,
-                                                               long long n, double* cx, double* cy, unsigned char* live) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    cx[i] = x0[i]; cy[i] = x1[i];
-    live[i] = collide_input_ok(x0[i], x1[i], x2[i], mass[i]) ? 1 : 0;
 }
 
 }  // namespace nb

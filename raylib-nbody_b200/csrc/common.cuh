@@ -96,6 +96,19 @@ __host__ __device__ inline Scale scale_for(unsigned int extent_bits, int mass_ex
     return s;
 }
 
+// Where a pack writes one generation of the j-stream: the device's own buffers and, in a single-process
+// multi-GPU context (nb_create_multi), the same buffers of every peer device — the all-gather of the packed
+// positions is done by the producing kernel's own stores over NVLink (peer memory), not by a collective.
+// extent[]: each device's copy of the rotating max|x| slots (max-reduced with peer atomics the same way).
+constexpr int kMaxPeers = 8;
+struct PeerSet {
+    int n;
+    float* pk[kMaxPeers];
+    float* lo[kMaxPeers];
+    GroupHdr* hdr[kMaxPeers];
+    unsigned int* extent[kMaxPeers];
+};
+
 // Epilogue modes of the force kernel.
 enum Mode : int {
     kForceOnly = 0,     // Physics::compute_gravity, Physics.hpp:183-261
@@ -121,10 +134,8 @@ struct StepParams {
     const float* pk_cur;        // pair-SoA j-stream being read (generation `gen`): hi parts
     const float* lo_cur;        // pair-SoA residuals {xl0,xl1,yl0,yl1,zl0,zl1,0,0}, read by the near path only
     const GroupHdr* hdr_cur;    // one per kGroupBodies stream rows
-    float* pk_next;             // generation gen+1, written by the epilogue
-    float* lo_next;
-    GroupHdr* hdr_next;
-    unsigned int* extent;       // kExtentSlots rotating slots of float bits
+    PeerSet out;                // generation gen+1, written by the epilogue (on every device of the context)
+    const unsigned int* extent; // kExtentSlots rotating slots of float bits (this device's copy; written through `out`)
     double* part;               // [1 + nseg][4][i_cap] FP64 partial sums: slot 0 carries sums between two
                                 // launches (local / remote sources), slots 1.. the source segments
     unsigned int* tile_counter; // [n_itiles] arrival counters (only nseg > 1)

@@ -31,7 +31,19 @@ struct Variant {
 
 }  // namespace nb
 
+struct nb_ctx;
+// A single-process multi-GPU context (nb_create_multi): one member context per device, member 0 is the
+// handle the caller holds. Members exchange the packed stream through peer memory (the packing kernels
+// store to every member's buffers) and order themselves with CUDA events; there is no NCCL on this path.
+struct nb_group {
+    std::vector<nb_ctx*> m;
+};
+
 struct nb_ctx {
+    nb_group* group = nullptr;           // non-null on every member of a multi-GPU context
+    cudaEvent_t ev_pub = nullptr;        // "my rows of the newest generation are in everyone's buffers, and I am
+                                         //  done reading the previous one" (recorded after each packing launch)
+    cudaEvent_t ev_bar = nullptr;        // team barriers around the rare multi-phase operations
     int device = 0;
     int rank = 0, world = 1;
     int sm_count = 148;
@@ -86,7 +98,9 @@ struct nb_ctx {
     long long overlap_grid_calls = 0;   // calls that took the O(N) grid broad phase
     void* merge_scratch = nullptr;      // nb_resolve_collisions: pair sink, current positions, hit list
     size_t merge_bytes = 0;
-    unsigned int* h_merge = nullptr;    // pinned: hit count + first hits of a rescan
+    void* replay_scratch = nullptr;     // merge_replay_kernel: sorted keys, heap, snapshots, log
+    size_t replay_bytes = 0;
+    long long merge_events = 0, merge_candidates = 0;  // of the last replay: events popped, bodies scanned
     long long merge_passes = 0;         // calls that found an overlap and replayed merges
     size_t staging_bytes = 0;
 
@@ -165,3 +179,23 @@ struct nb_ctx {
         return s;
     }
 };
+
+namespace nb {
+
+// ---- the team behind a handle ---------------------------------------------------------------------
+// A plain or NCCL-sharded context is a team of one. The handle of a single-process multi-GPU context
+// (nb_create_multi) is member 0 of its group; every operation below enqueues its phases member by member.
+struct Team {
+    nb_ctx* solo[1];
+    nb_ctx** first;
+    size_t count;
+    explicit Team(nb_ctx* c) {
+        solo[0] = c;
+        if (c && c->group) { first = c->group->m.data(); count = c->group->m.size(); }
+        else { first = solo; count = 1; }
+    }
+    nb_ctx** begin() const { return first; }
+    nb_ctx** end() const { return first + count; }
+};
+
+}  // namespace nb

@@ -20,7 +20,7 @@ constexpr int kDiagExtentSlot = kExtentSlots;  // extra slot after the rotating 
 
 __global__ void __launch_bounds__(kDiagThreads) diag_extent_kernel(const double* x0, const double* x1,
                                                                    const double* x2, long long lo, long long hi,
-                                                                   unsigned int* extent) {
+                                                                   PeerSet out) {
     __shared__ float red[kDiagThreads / 32];
     float e = 0.f;
     for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(kDiagThreads) diag_extent_kernel(const double*
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < kDiagThreads / 32; ++w) e = fmaxf(e, red[w]);
-        atomicMax(&extent[kDiagExtentSlot], __float_as_uint(e));
+        for (int q = 0; q < out.n; ++q) atomicMax(&out.extent[q][kDiagExtentSlot], __float_as_uint(e));
     }
 }
 

@@ -43,8 +43,7 @@ __device__ __forceinline__ float extent_of(const double (&x)[3], bool live) {
 // and half-extents; every row is stored as hi = float((x - c) * 2^-e), lo = float of the rest.
 // `sbox` is shared scratch of 6 floats per warp. All threads of the CTA must call this.
 template <int NT>
-__device__ __forceinline__ void pack_group(float* __restrict__ pk, float* __restrict__ lo_stream,
-                                           GroupHdr* __restrict__ hdr, long long row, const double (&x)[3], float m,
+__device__ __forceinline__ void pack_group(const PeerSet& out, long long row, const double (&x)[3], float m,
                                            bool attracts, double inv_len, double inv_mass, float (*sbox)[6]) {
     static_assert(NT == kGroupBodies, "one thread per row of a group");
     const int tid = threadIdx.x;
@@ -89,31 +88,38 @@ __device__ __forceinline__ void pack_group(float* __restrict__ pk, float* __rest
     double cs[3];  // the origin in packed units (exact: power-of-two scale) — what the readers subtract
 #pragma unroll
     for (int k = 0; k < 3; ++k) cs[k] = __dmul_rn(c[k], inv_len);
-    float* rec = pk + (row >> 1) * 8 + (row & 1);
-    float* rlo = lo_stream + (row >> 1) * 8 + (row & 1);
     // rows dropped by the gather filter (and padding rows) sit at hi_x = 2^60 packed units with m = 0:
     // r^6 overflows to +inf, rsqrt(+inf) = +0, so they contribute exactly 0 even to the kernels that
     // do not multiply by the mass (uniform-mass variants)
+    float fh[3], fl[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const double d = __dadd_rn(__dmul_rn(x[k], inv_len), -cs[k]);
-        const float fh = (float)d;
-        const float fl = (float)__dadd_rn(d, -(double)fh);
-        rec[2 * k] = attracts ? fh : (k == 0 ? kFarPacked : 0.f);
-        rlo[2 * k] = attracts ? fl : 0.f;
+        const float h1 = (float)d;
+        fh[k] = attracts ? h1 : (k == 0 ? kFarPacked : 0.f);
+        fl[k] = attracts ? (float)__dadd_rn(d, -(double)h1) : 0.f;
     }
-    rec[6] = attracts ? (float)__dmul_rn((double)m, inv_mass) : 0.f;
-    rlo[6] = 0.f;
-    if (tid == 0) {
-        GroupHdr g;
+    const float fm = attracts ? (float)__dmul_rn((double)m, inv_mass) : 0.f;
+    GroupHdr g;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        g.c[k] = cs[k];
+        g.h[k] = any ? h[k] : 0.f;
+    }
+    g.reach = any ? kNearFactor * fmaxf(h[0], fmaxf(h[1], h[2])) : 0.f;
+    g.pad[0] = g.pad[1] = 0.f;
+    const long long off = (row >> 1) * 8 + (row & 1);
+    for (int q = 0; q < out.n; ++q) {  // this device, then every peer (stores over NVLink)
+        float* rec = out.pk[q] + off;
+        float* rlo = out.lo[q] + off;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            g.c[k] = cs[k];
-            g.h[k] = any ? h[k] : 0.f;
+            rec[2 * k] = fh[k];
+            rlo[2 * k] = fl[k];
         }
-        g.reach = any ? kNearFactor * fmaxf(h[0], fmaxf(h[1], h[2])) : 0.f;
-        g.pad[0] = g.pad[1] = 0.f;
-        hdr[row / kGroupBodies] = g;
+        rec[6] = fm;
+        rlo[6] = 0.f;
+        if (tid == 0) out.hdr[q][row / kGroupBodies] = g;
     }
 }
 

@@ -30,6 +30,10 @@
 namespace nb {
 
 constexpr int kUnrollPairs = NB_UNROLL_PAIRS;
+#ifndef NB_NEAR_UNROLL
+#define NB_NEAR_UNROLL 4
+#endif
+constexpr int kNearUnroll = NB_NEAR_UNROLL;  // pair records per loop body of the near path
 
 // float -> double of a chunk sum. F2F.F64.F32 runs on the XU pipe next to the kernel's MUFU.RSQ stream
 // (one conversion costs as much XU time as a MUFU); NB_INT_FLUSH builds the double from the float's bits
@@ -199,7 +203,7 @@ __device__ __forceinline__ void chunk_interact_near(Target<POT, EQM, D2, PONLY> 
                                                     float eps2, long long j_first, long long row0) {
     const f2 e2 = f2_make(eps2, eps2);
     const f2 zero = f2_make(0.f, 0.f);
-#pragma unroll 4
+#pragma unroll kNearUnroll
     for (int u = 0; u < CH / 2; ++u) {
         f2 xj, yj, zj, mj, xl, yl, zl, unused;
         load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);

@@ -22,6 +22,10 @@
 #include "epilogue.cuh"
 #include "force.cuh"
 
+#ifndef NB_FLUSH_PER_GROUP
+#define NB_FLUSH_PER_GROUP 1  // 1: fold the FP32 sums into FP64 once per 128-source group instead of per 64-source chunk
+#endif
+
 namespace nb {
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -71,17 +75,17 @@ force_kernel(const __grid_constant__ StepParams p) {
     cur.pot_unit *= p.eqm_mass;
 
     // ---- targets ---------------------------------------------------------------------
+    // Rows past the rank's last target get a position no group can be "near" (their sums are never stored),
+    // so the per-group loop below carries no validity test.
     Tg tg[R];
     double S[R][4];
-    unsigned valid_mask = 0;  // bit r: row row0 + r*NT + tid is a target of this rank
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const long long row = rbase + 32 * r;
         const bool ok = row < p.i_hi;
-        if (ok) valid_mask |= 1u << r;
         const long long body = ok ? (long long)p.order[row] : -1;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = ok ? __dmul_rn(p.x[k][body], cur.inv_len) : 0.0;
+        for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = ok ? __dmul_rn(p.x[k][body], cur.inv_len) : 1.0e300;
         tg[r].reset();
         S[r][0] = S[r][1] = S[r][2] = S[r][3] = 0.0;
     }
@@ -137,7 +141,7 @@ force_kernel(const __grid_constant__ StepParams p) {
                 tg[r].set_offset(f0, f1, f2v);
                 const bool inside = (fabsf(f0) < hb.x + hb.w) && (fabsf(f1) < hb.y + hb.w) &&
                                     (D2 || fabsf(f2v) < hb.z + hb.w);
-                near = near || (inside && ((valid_mask >> r) & 1u));
+                near = near || inside;
             }
             const float4* grec = &ring[s][g * kGroupBodies];
             const long long j_group = j_tile + (long long)g * kGroupBodies;
@@ -154,15 +158,24 @@ force_kernel(const __grid_constant__ StepParams p) {
                         chunk_interact<R, POT, true, CH, EQM, D2, PONLY, 32>(tg, rec, cur.eps2, j_first, rbase);
                     else
                         chunk_interact<R, POT, false, CH, EQM, D2, PONLY, 32>(tg, rec, cur.eps2, j_first, rbase);
+#if !NB_FLUSH_PER_GROUP
 #pragma unroll
                     for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+#endif
                 }
+#if NB_FLUSH_PER_GROUP
+#pragma unroll
+                for (int r = 0; r < R; ++r) tg[r].flush(S[r][0], S[r][1], S[r][2], S[r][3]);
+#endif
             } else {
                 // ---- near group: two-float offsets on both sides, RN targets at a time ------------
                 // (developer counter of nb_near_stats: kept out of the common path, where a lane-divergent
                 // statement would cost the hot loop its uniform-register addressing)
                 if (p.stats && (tid & 31) == 0) atomicAdd(&p.stats[1], 1ull);
-                constexpr int RN = R >= 2 ? 2 : 1;
+#ifndef NB_NEAR_RN
+#define NB_NEAR_RN 2
+#endif
+                constexpr int RN = R >= NB_NEAR_RN ? NB_NEAR_RN : (R >= 2 ? 2 : 1);
                 const float4* glo = reinterpret_cast<const float4*>(p.lo_cur) + j_group;
 #pragma unroll 1
                 for (int c = 0; c < kChunksPerGroup; ++c) {
@@ -234,7 +247,7 @@ force_kernel(const __grid_constant__ StepParams p) {
     if (p.nseg > 1) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (!((valid_mask >> r) & 1u)) continue;
+            if (rbase + 32 * r >= p.i_hi) continue;
             const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
             for (int c = C0; c < NC; ++c) __stcg(&p.part[((long long)(1 + js) * 4 + c) * p.i_cap + col], S[r][c]);
@@ -251,7 +264,7 @@ force_kernel(const __grid_constant__ StepParams p) {
         __threadfence();
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (!((valid_mask >> r) & 1u)) continue;
+            if (rbase + 32 * r >= p.i_hi) continue;
             const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
             for (int c = C0; c < NC; ++c) {
@@ -264,7 +277,7 @@ force_kernel(const __grid_constant__ StepParams p) {
     if (p.accumulate) {  // partial sums left by an earlier launch over other sources
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (!((valid_mask >> r) & 1u)) continue;
+            if (rbase + 32 * r >= p.i_hi) continue;
             const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
             for (int c = C0; c < NC; ++c) S[r][c] += __ldcg(&p.part[(long long)c * p.i_cap + col]);
@@ -273,7 +286,7 @@ force_kernel(const __grid_constant__ StepParams p) {
     if (p.mode == kPartialOnly) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            if (!((valid_mask >> r) & 1u)) continue;
+            if (rbase + 32 * r >= p.i_hi) continue;
             const long long col = rbase + 32 * r - p.i_lo;
 #pragma unroll
             for (int c = C0; c < NC; ++c) p.part[(long long)c * p.i_cap + col] = S[r][c];
@@ -296,7 +309,7 @@ force_kernel(const __grid_constant__ StepParams p) {
         nx.x[0] = nx.x[1] = nx.x[2] = 0.0;
         nx.m = 0.f;
         nx.attracts = false;
-        if ((valid_mask >> r) & 1u) body_epilogue<POT>(p, (long long)p.order[rbase + 32 * r], S[r], cur, dg, nx);
+        if (rbase + 32 * r < p.i_hi) body_epilogue<POT>(p, (long long)p.order[rbase + 32 * r], S[r], cur, dg, nx);
         if (packs) {  // hand the row's next position to the pack below (which groups rows by 128, not by warp)
 #pragma unroll
             for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = nx.x[k];
@@ -313,7 +326,7 @@ force_kernel(const __grid_constant__ StepParams p) {
             const double nx3[3] = {tpos[0][q * NT + tid], tpos[1][q * NT + tid], tpos[2][q * NT + tid]};
             const bool att = tatt[q * NT + tid] != 0;
             ext = fmaxf(ext, extent_of(nx3, att));
-            pack_group<NT>(p.pk_next, p.lo_next, p.hdr_next, row0 + (long long)q * NT + tid, nx3, tmass[q * NT + tid], att,
+            pack_group<NT>(p.out, row0 + (long long)q * NT + tid, nx3, tmass[q * NT + tid], att,
                            nxt.inv_len, inv_mass, sbox);
         }
     }
@@ -333,10 +346,10 @@ force_kernel(const __grid_constant__ StepParams p) {
     if (tid == 0 && packs) {
         float e = 0.f;
         for (int w = 0; w < kWarps; ++w) e = fmaxf(e, red_ext[w]);
-        atomicMax(&p.extent[(p.gen + 1) % kExtentSlots], __float_as_uint(e));
+        for (int q = 0; q < p.out.n; ++q) atomicMax(&p.out.extent[q][(p.gen + 1) % kExtentSlots], __float_as_uint(e));
         // recycled by the one CTA that always reaches this epilogue for target tile 0 (with nseg > 1 that is
-        // the last arrival of the tile's segments, whichever segment it carries)
-        if (it == 0) p.extent[(p.gen + 2) % kExtentSlots] = 0u;
+        // the last arrival of the tile's segments, whichever segment it carries); own copy only
+        if (it == 0) p.out.extent[0][(p.gen + 2) % kExtentSlots] = 0u;
     }
     if (POT && tid < 10) {
         double acc = 0.0;

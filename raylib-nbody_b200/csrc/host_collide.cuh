@@ -49,8 +49,16 @@ GridSpec plan_grid(int dim, const double lo[3], const double hi[3], double r_max
 
 // Detection over all pairs (all-pairs sweep or grid broad phase). d_pairs (optional, device): sink for the
 // overlapping pairs' keys i * n + j; *n_emitted = how many the kernels tried to append.
+struct GridUse {  // what the broad phase built (valid until the next call that touches collide_scratch)
+    GridSpec g{};
+    const unsigned int* cell_start = nullptr;
+    const unsigned int* sorted_idx = nullptr;
+    double r_max = 0.0;
+};
+
 static int overlaps_impl(nb_ctx* c, const double* radius, int64_t* n_overlaps, int64_t* first_pair,
-                         unsigned long long* d_pairs, unsigned long long pair_cap, unsigned long long* n_emitted) {
+                         unsigned long long* d_pairs, unsigned long long pair_cap, unsigned long long* n_emitted,
+                         GridUse* used = nullptr) {
     NB_CUDA(cudaSetDevice(c->device));
     const long long n = c->n;
     const StateView s = c->view();
@@ -116,6 +124,11 @@ static int overlaps_impl(nb_ctx* c, const double* radius, int64_t* n_overlaps, i
                                                                       cell_start, sorted_idx, d_res, d_pairs, pair_cap);
         c->kernel_launches += 4;
         c->overlap_grid_calls++;
+        if (used) {
+            used->g = g;
+            used->cell_start = cell_start;
+            used->sorted_idx = sorted_idx;
+        }
     } else {
         if (c->dim == 2)
             overlap_kernel<true><<<blocks_for(n, kOverlapThreads), kOverlapThreads, 0, c->stream>>>(
@@ -126,6 +139,7 @@ static int overlaps_impl(nb_ctx* c, const double* radius, int64_t* n_overlaps, i
         c->kernel_launches++;
     }
     NB_CUDA(cudaGetLastError());
+    if (used) used->r_max = r_max;
     unsigned long long res[3];
     NB_CUDA(cudaMemcpyAsync(res, d_res, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
@@ -148,14 +162,11 @@ extern "C" int nb_count_overlaps(nb_ctx* c, const double* radius, int64_t* n_ove
     return overlaps_impl(c, radius, n_overlaps, first_pair, nullptr, 0, nullptr);
 }
 
-// Collision::resolve in its default merge mode (Collision.hpp:49-132). The pair tests run on the device; the
-// merges are replayed on the host in the reference's visiting order as an event queue:
-//   * pairs whose two bodies are untouched so far behave as the initial detection says;
-//   * every merge changes exactly one snapshot (the survivor's): the device re-tests that body against all
-//     living bodies (collide_rescan_kernel) and the hits that still lie AHEAD in the (i, j) order are queued;
-//   * an event is re-tested with the current snapshots when its turn comes.
-// Any pair that overlaps when the reference would test it was detected either initially or by the rescan that
-// followed the last change of one of its bodies, so the replay performs exactly the reference's merges.
+// Collision::resolve in its default merge mode (Collision.hpp:49-132), entirely on the device: the kernels of
+// collide.cuh detect the initially overlapping pairs, merge_replay_kernel (merge.cuh) replays the merges in the
+// reference's visiting order as an event queue — re-tests, merge arithmetic (incl. the radius' cbrt) and the
+// neighbourhood scans after every merge — with no host round trip per merge. The host only stages the caller's
+// radii/densities, sorts the initial pair keys (cub) and reads the outcome back.
 extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const double* density, int64_t* n_merges,
                                      uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
                                      uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap) {
@@ -169,140 +180,138 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
     if (!radius || !density || !pos_xy || !vel_xy || !mass || !pinned || !radius_out)
         return fail(NB_ERR_INVALID, "nb_resolve_collisions: null array");
     NB_CUDA(cudaSetDevice(c->device));
+    if (merge_log_cap < 0 || !merge_log) merge_log_cap = 0;
 
-    // scratch of the merge phase: pair sink | cx | cy | hits | live | hit counter
+    // ---- detection: every overlapping pair's key i * n + j into the head of the merge scratch -----------
     unsigned long long pair_cap = (unsigned long long)std::max<long long>(4 * n, 1 << 16);
     int64_t overlaps = 0;
     unsigned long long emitted = 0;
-    constexpr long long kMergeFirstHits = 64;  // count + this many hits ride in the first readback
-    size_t off_cx = 0, off_cy = 0, off_hits = 0, off_live = 0, off_cnt = 0;
+    GridUse used;
     for (;;) {
-        off_cx = align256(sizeof(unsigned long long) * pair_cap);
-        off_cy = off_cx + align256(sizeof(double) * (size_t)n);
-        off_hits = off_cy + align256(sizeof(double) * (size_t)n);
-        off_live = off_hits + align256(sizeof(unsigned int) * ((size_t)n + 1));
-        off_cnt = off_live + align256((size_t)n);
-        const size_t total = off_cnt + 256;
-        if (total > c->merge_bytes) {
+        const size_t need = align256(sizeof(unsigned long long) * pair_cap);
+        if (need > c->merge_bytes) {
             NB_CUDA(cudaStreamSynchronize(c->stream));
             if (c->merge_scratch) cudaFree(c->merge_scratch);
             c->merge_scratch = nullptr;
             c->merge_bytes = 0;
-            NB_CUDA(cudaMalloc(&c->merge_scratch, total));
-            c->merge_bytes = total;
+            NB_CUDA(cudaMalloc(&c->merge_scratch, need));
+            c->merge_bytes = need;
         }
+        used = GridUse{};
         NB_TRY(overlaps_impl(c, radius, &overlaps, nullptr, static_cast<unsigned long long*>(c->merge_scratch), pair_cap,
-                             &emitted));
+                             &emitted, &used));
         if (emitted <= pair_cap) break;
         pair_cap = emitted + 1024;  // more overlapping pairs than the sink held: once more with room for all
     }
     if (overlaps == 0) return NB_OK;  // the common frame: resolve() changes nothing
 
-    char* mb = static_cast<char*>(c->merge_scratch);
-    double* d_cx = reinterpret_cast<double*>(mb + off_cx);
-    double* d_cy = reinterpret_cast<double*>(mb + off_cy);
-    unsigned int* d_hits = reinterpret_cast<unsigned int*>(mb + off_hits);  // [0]: running hit total, [1..]: this launch's hits
-    unsigned char* d_live = reinterpret_cast<unsigned char*>(mb + off_live);
-    double* d_cr = reinterpret_cast<double*>(static_cast<char*>(c->collide_scratch) + 256);  // the radii overlaps_impl staged
-
-    // host snapshots (Collision.hpp:51-67): everything the merges read and write
-    std::vector<unsigned long long> keys((size_t)emitted);
-    NB_CUDA(cudaMemcpyAsync(keys.data(), c->merge_scratch, sizeof(unsigned long long) * (size_t)emitted, cudaMemcpyDeviceToHost,
-                            c->stream));
-    const StateView sv = c->view();
-    collide_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], c->mass, n, d_cx, d_cy, d_live);
-    NB_CUDA(cudaMemsetAsync(d_hits, 0, sizeof(unsigned int), c->stream));
-    c->kernel_launches++;
-    if (!c->h_merge) NB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_merge), sizeof(unsigned int) * kMergeFirstHits));
-    std::vector<double> hp(2 * (size_t)n), hv(2 * (size_t)n), hr(radius, radius + n);
-    std::vector<float> hm((size_t)n);
-    std::vector<uint8_t> hpin((size_t)n), hlive((size_t)n);
-    NB_TRY(download_dim(c, hp.data(), hv.data(), nullptr, 2));
-    NB_CUDA(cudaMemcpyAsync(hm.data(), c->mass, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaMemcpyAsync(hpin.data(), c->pinned, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaMemcpyAsync(hlive.data(), d_live, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-
-    std::set<unsigned long long> events(keys.begin(), keys.end());
-    std::vector<unsigned int> hits((size_t)n);
-    const unsigned long long un = (unsigned long long)n;
-    const double pi = 3.141592653589793238462643383279502884;  // std::numbers::pi
-    long long cur_row = -1;
-    bool row_alive = false;
-    int64_t merges = 0;
-    unsigned int hit_base = 0;
-    while (!events.empty()) {
-        const unsigned long long key = *events.begin();
-        events.erase(events.begin());
-        const long long a = (long long)(key / un), b = (long long)(key % un);
-        if (a != cur_row) {  // alive[i] is looked at when row i starts and not again (:76)
-            cur_row = a;
-            row_alive = alive[a] != 0;
-        }
-        if (!row_alive || !alive[b]) continue;  // :76, :78
-        const double dx = hp[2 * b] - hp[2 * a];
-        const double dy = hp[2 * b + 1] - hp[2 * a + 1];
-        const double rsum = hr[a] + hr[b];
-        const double dist2 = dx * dx + dy * dy;
-        if (dist2 > rsum * rsum) continue;  // :85, with the snapshots as they are NOW
-        const bool a_survives = (hm[a] >= hm[b]) || hpin[b];  // :94
-        const long long sv_i = a_survives ? a : b, dd = a_survives ? b : a;
-        if (hpin[dd] && hpin[sv_i]) continue;  // :97-104
-        const double ms = (double)hm[sv_i], md = (double)hm[dd];
-        const double M = ms + md;                                            // :107
-        const double px = ms * hv[2 * sv_i] + md * hv[2 * dd];               // :108-109
-        const double py = ms * hv[2 * sv_i + 1] + md * hv[2 * dd + 1];
-        const double xx = (ms * hp[2 * sv_i] + md * hp[2 * dd]) / M;         // :111-112
-        const double xy = (ms * hp[2 * sv_i + 1] + md * hp[2 * dd + 1]) / M;
-        hm[sv_i] = (float)M;                                                 // :115,128
-        hv[2 * sv_i] = px / M;                                               // :110,116
-        hv[2 * sv_i + 1] = py / M;
-        hp[2 * sv_i] = xx;
-        hp[2 * sv_i + 1] = xy;
-        hpin[sv_i] = (hpin[sv_i] || hpin[dd]) ? 1 : 0;                       // :120,131
-        hr[sv_i] = std::cbrt((3.0 * std::max(1.0, (double)hm[sv_i])) / (4.0 * pi * density[sv_i]));  // :37-46,132
-        changed[sv_i] = 1;
-        const bool newly_dead = alive[dd] != 0;
-        alive[dd] = 0;                                                       // :124-125
-        if (merge_log && merges < merge_log_cap) {
-            merge_log[2 * merges] = sv_i;
-            merge_log[2 * merges + 1] = dd;
-        }
-        ++merges;
-        // which living bodies does the survivor's new state reach? One launch, one readback of the count and
-        // the first hits into pinned memory; the (rare) long hit lists take a second copy.
-        collide_rescan_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d_cx, d_cy, d_cr, d_live, n, sv_i, xx, xy, hr[sv_i],
-                                                                       newly_dead ? dd : -1, d_hits, hit_base);
-        c->kernel_launches++;
-        const size_t first = (size_t)std::min<long long>(kMergeFirstHits, n + 1);
-        NB_CUDA(cudaMemcpyAsync(c->h_merge, d_hits, sizeof(unsigned int) * first, cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
-        const unsigned int n_hits = c->h_merge[0] - hit_base;
-        hit_base = c->h_merge[0];
-        const unsigned int* hit = c->h_merge + 1;
-        if ((size_t)n_hits + 1 > first) {
-            NB_CUDA(cudaMemcpyAsync(hits.data(), d_hits + 1, sizeof(unsigned int) * n_hits, cudaMemcpyDeviceToHost, c->stream));
+    // ---- replay scratch (its own allocation: the pair sink above stays where it is) ------------------------
+    unsigned long long heap_cap = (unsigned long long)std::max<long long>(8 * n, 1 << 20);
+    for (int attempt = 0;; ++attempt) {
+        size_t cub_bytes = 0;
+        NB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                               (int)emitted, 0, 64, c->stream));
+        size_t off = 0;
+        auto take = [&](size_t bytes) { const size_t at = off; off += align256(bytes); return at; };
+        const size_t o_sorted = take(8 * (size_t)emitted), o_cub = take(cub_bytes), o_heap = take(8 * (size_t)heap_cap),
+                     o_cx = take(8 * (size_t)n), o_cy = take(8 * (size_t)n), o_vx = take(8 * (size_t)n),
+                     o_vy = take(8 * (size_t)n), o_rho = take(8 * (size_t)n), o_cm = take(4 * (size_t)n),
+                     o_hits = take(4 * (size_t)n), o_pin = take((size_t)n), o_alive = take((size_t)n),
+                     o_live = take((size_t)n), o_changed = take((size_t)n), o_log = take(16 * (size_t)std::max<int64_t>(merge_log_cap, 1)),
+                     o_out = take(64);
+        if (off > c->replay_bytes) {
             NB_CUDA(cudaStreamSynchronize(c->stream));
-            hit = hits.data();
+            if (c->replay_scratch) cudaFree(c->replay_scratch);
+            c->replay_scratch = nullptr;
+            c->replay_bytes = 0;
+            NB_CUDA(cudaMalloc(&c->replay_scratch, off));
+            c->replay_bytes = off;
         }
-        for (unsigned int h = 0; h < n_hits; ++h) {
-            const unsigned long long k = hit[h];
-            const unsigned long long lo = std::min<unsigned long long>(k, (unsigned long long)sv_i);
-            const unsigned long long hi = std::max<unsigned long long>(k, (unsigned long long)sv_i);
-            const unsigned long long nk = lo * un + hi;
-            if (nk > key) events.insert(nk);  // only tests the reference has not made yet
+        char* rb = static_cast<char*>(c->replay_scratch);
+        unsigned long long* d_sorted = reinterpret_cast<unsigned long long*>(rb + o_sorted);
+        NB_CUDA(cub::DeviceRadixSort::SortKeys(rb + o_cub, cub_bytes, static_cast<unsigned long long*>(c->merge_scratch), d_sorted,
+                                               (int)emitted, 0, 64, c->stream));
+        MergeParams mp{};
+        mp.n = n;
+        mp.cx = reinterpret_cast<double*>(rb + o_cx); mp.cy = reinterpret_cast<double*>(rb + o_cy);
+        mp.vx = reinterpret_cast<double*>(rb + o_vx); mp.vy = reinterpret_cast<double*>(rb + o_vy);
+        mp.cr = reinterpret_cast<double*>(static_cast<char*>(c->collide_scratch) + 256);  // the radii overlaps_impl staged
+        mp.cm = reinterpret_cast<float*>(rb + o_cm);
+        mp.pin = reinterpret_cast<unsigned char*>(rb + o_pin);
+        mp.alive = reinterpret_cast<unsigned char*>(rb + o_alive);
+        mp.live = reinterpret_cast<unsigned char*>(rb + o_live);
+        mp.changed = reinterpret_cast<unsigned char*>(rb + o_changed);
+        double* d_rho = reinterpret_cast<double*>(rb + o_rho);
+        mp.density = d_rho;
+        const StateView sv = c->view();
+        mp.x_init = sv.x[0]; mp.y_init = sv.x[1];
+        mp.initial = d_sorted; mp.n_initial = emitted;
+        mp.heap = reinterpret_cast<unsigned long long*>(rb + o_heap); mp.heap_cap = heap_cap;
+        mp.hits = reinterpret_cast<unsigned int*>(rb + o_hits);
+        mp.g = used.g; mp.cell_start = used.cell_start; mp.sorted_idx = used.sorted_idx; mp.r_max = used.r_max;
+        mp.merge_log = reinterpret_cast<long long*>(rb + o_log); mp.merge_log_cap = merge_log_cap;
+        mp.out = reinterpret_cast<long long*>(rb + o_out);
+        NB_CUDA(cudaMemcpyAsync(d_rho, density, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        if (attempt > 0)  // a retry starts from the caller's radii again (the first replay grew the survivors')
+            NB_CUDA(cudaMemcpyAsync(mp.cr, radius, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        merge_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], sv.v[0], sv.v[1], c->mass,
+                                                                        c->pinned, n, mp);
+        merge_replay_kernel<<<1, kMergeThreads, 0, c->stream>>>(mp);
+        NB_CUDA(cudaGetLastError());
+        c->kernel_launches += 2;
+        long long out[4] = {0, 0, 0, 0};
+        NB_CUDA(cudaMemcpyAsync(out, mp.out, sizeof(out), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (out[1] != 0) {  // the event heap overflowed: replay again with a larger one
+            if (attempt >= 6) return fail(NB_ERR_INVALID, "nb_resolve_collisions: event queue kept overflowing");
+            heap_cap *= 4;
+            continue;
         }
+        const int64_t merges = out[0];
+        c->merge_events = out[2];
+        c->merge_candidates = out[3];
+        // ---- the outcome: dead bodies, survivors' new components, the merges in order ----------------------------
+        std::vector<double> hx((size_t)n), hy((size_t)n), hvx((size_t)n), hvy((size_t)n), hr((size_t)n);
+        NB_CUDA(cudaMemcpyAsync(alive, mp.alive, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(changed, mp.changed, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hx.data(), mp.cx, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hy.data(), mp.cy, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hvx.data(), mp.vx, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hvy.data(), mp.vy, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hr.data(), mp.cr, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        std::vector<float> hm((size_t)n);
+        std::vector<uint8_t> hpin((size_t)n);
+        NB_CUDA(cudaMemcpyAsync(hm.data(), mp.cm, 4 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(hpin.data(), mp.pin, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        const int64_t logged = std::min<int64_t>(merges, merge_log_cap);
+        if (logged > 0)
+            NB_CUDA(cudaMemcpyAsync(merge_log, mp.merge_log, 16 * (size_t)logged, cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        for (long long i = 0; i < n; ++i) {
+            if (!changed[i]) continue;
+            pos_xy[2 * i] = hx[(size_t)i]; pos_xy[2 * i + 1] = hy[(size_t)i];
+            vel_xy[2 * i] = hvx[(size_t)i]; vel_xy[2 * i + 1] = hvy[(size_t)i];
+            mass[i] = hm[(size_t)i];
+            pinned[i] = hpin[(size_t)i];
+            radius_out[i] = hr[(size_t)i];
+        }
+        *n_merges = merges;
+        c->merge_passes++;
+        return NB_OK;
     }
-    NB_CUDA(cudaGetLastError());
-    for (long long i = 0; i < n; ++i) {
-        if (!changed[i]) continue;
-        pos_xy[2 * i] = hp[2 * i]; pos_xy[2 * i + 1] = hp[2 * i + 1];
-        vel_xy[2 * i] = hv[2 * i]; vel_xy[2 * i + 1] = hv[2 * i + 1];
-        mass[i] = hm[i];
-        pinned[i] = hpin[i];
-        radius_out[i] = hr[i];
-    }
-    *n_merges = merges;
-    c->merge_passes++;
+}
+
+// glibc's cbrt restated for the device (merge.cuh), for the test that pins it against libm.
+extern "C" int nb_debug_cbrt(nb_ctx* c, const double* in, double* out, int64_t n) {
+    if (!c || !in || !out || n < 0) return fail(NB_ERR_INVALID, "nb_debug_cbrt: bad arguments");
+    if (n == 0) return NB_OK;
+    NB_CUDA(cudaSetDevice(c->device));
+    double* d = nullptr;
+    NB_CUDA(cudaMalloc(&d, 16 * (size_t)n));
+    NB_CUDA(cudaMemcpyAsync(d, in, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    cbrt_probe_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(d, d + n, (int)n);
+    NB_CUDA(cudaMemcpyAsync(out, d + n, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d);
     return NB_OK;
 }

@@ -17,6 +17,7 @@
 
 #include "bh.cuh"
 #include "collide.cuh"
+#include "merge.cuh"
 #include "ctx.cuh"
 #include "diag.cuh"
 #include "exact.cuh"
@@ -394,6 +395,64 @@ extern "C" int nb_default_config(nb_config* out) {
     return NB_OK;
 }
 
+static void destroy_one(nb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+    free_bodies(c);
+    cudaFree(c->extent);
+    cudaFree(c->l2_scratch);
+    cudaFree(c->collide_scratch);
+    cudaFree(c->bh_scratch);
+    cudaFree(c->merge_scratch);
+    cudaFree(c->replay_scratch);
+    cudaFree(c->near_stats);
+    if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
+    cudaFree(c->totals);
+    if (c->h_totals) cudaFreeHost(c->h_totals);
+    for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
+    cudaEvent_t evs[] = {c->ev_timer0, c->ev_timer1, c->ev_packed, c->ev_gathered, c->ev_comm0[0], c->ev_comm0[1],
+                         c->ev_comm1[0], c->ev_comm1[1], c->ev_own0, c->ev_own1, c->ev_pub, c->ev_bar};
+    for (cudaEvent_t e : evs)
+        if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    delete c;
+}
+
+static int init_ctx(nb_ctx* c, int world) {
+    nb_default_config(&c->cfg);
+    int lo_prio = 0, hi_prio = 0;
+    cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+    NB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    NB_CUDA(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, hi_prio));
+    NB_CUDA(cudaEventCreate(&c->ev_timer0));
+    NB_CUDA(cudaEventCreate(&c->ev_timer1));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_pub, cudaEventDisableTiming));
+    NB_CUDA(cudaEventCreateWithFlags(&c->ev_bar, cudaEventDisableTiming));
+    for (int g = 0; g < 2; ++g) {
+        NB_CUDA(cudaEventCreate(&c->ev_comm0[g]));
+        NB_CUDA(cudaEventCreate(&c->ev_comm1[g]));
+    }
+    NB_CUDA(cudaEventCreate(&c->ev_own0));
+    NB_CUDA(cudaEventCreate(&c->ev_own1));
+    NB_CUDA(cudaMalloc(&c->extent, sizeof(unsigned int) * (kExtentSlots + 4)));
+    NB_CUDA(cudaMemset(c->extent, 0, sizeof(unsigned int) * (kExtentSlots + 4)));
+    // [0,16): this rank's fixed-order sums; [16, 16 + kDiagValues * world): every rank's, all-gathered
+    const size_t totals_len = 48 + (size_t)kDiagValues * world + 16;
+    NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * totals_len));
+    NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * totals_len));
+    if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
+    if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
+    if (const char* v = getenv("NB_RESORT_EVERY")) c->resort_every = std::max(1, atoi(v));
+    if (const char* v = getenv("NB_FORCE_GENERIC")) c->force_generic = atoi(v) != 0;
+    return NB_OK;
+}
+
 static int create_common(int device, int rank, int world, nb_ctx** out) {
     if (!out) return fail(NB_ERR_INVALID, "nb_create: null out pointer");
     *out = nullptr;
@@ -413,31 +472,11 @@ static int create_common(int device, int rank, int world, nb_ctx** out) {
     c->rank = rank;
     c->world = world;
     c->sm_count = prop.multiProcessorCount;
-    nb_default_config(&c->cfg);
-    int lo_prio = 0, hi_prio = 0;
-    cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
-    NB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    NB_CUDA(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, hi_prio));
-    NB_CUDA(cudaEventCreate(&c->ev_timer0));
-    NB_CUDA(cudaEventCreate(&c->ev_timer1));
-    NB_CUDA(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
-    NB_CUDA(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
-    for (int g = 0; g < 2; ++g) {
-        NB_CUDA(cudaEventCreate(&c->ev_comm0[g]));
-        NB_CUDA(cudaEventCreate(&c->ev_comm1[g]));
+    const int rc = init_ctx(c, world);
+    if (rc != NB_OK) {  // nothing half-built survives a failed creation
+        destroy_one(c);
+        return rc;
     }
-    NB_CUDA(cudaEventCreate(&c->ev_own0));
-    NB_CUDA(cudaEventCreate(&c->ev_own1));
-    NB_CUDA(cudaMalloc(&c->extent, sizeof(unsigned int) * (kExtentSlots + 4)));
-    NB_CUDA(cudaMemset(c->extent, 0, sizeof(unsigned int) * (kExtentSlots + 4)));
-    // [0,16): this rank's fixed-order sums; [16, 16 + kDiagValues * world): every rank's, all-gathered
-    const size_t totals_len = 16 + (size_t)kDiagValues * world + 16;
-    NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * totals_len));
-    NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * totals_len));
-    if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
-    if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
-    if (const char* v = getenv("NB_RESORT_EVERY")) c->resort_every = std::max(1, atoi(v));
-    if (const char* v = getenv("NB_FORCE_GENERIC")) c->force_generic = atoi(v) != 0;
     *out = c;
     return NB_OK;
 }
@@ -466,37 +505,71 @@ extern "C" int nb_create_sharded(int device, int rank, int world, const void* nc
     return NB_OK;
 }
 
+// One process, several GPUs (the reference is one process, src/main.cpp:100-143): member i owns the i-th
+// slice of the targets exactly as rank i of a sharded context does (nb_partition), but the members exchange
+// the packed stream through peer memory — the packing kernels store straight into every member's buffers
+// over NVLink — and order themselves with CUDA events. No NCCL, no torchrun.
+extern "C" int nb_create_multi(const int* devices, int n_dev, nb_ctx** out) {
+    if (!out || !devices) return fail(NB_ERR_INVALID, "nb_create_multi: null");
+    *out = nullptr;
+    if (n_dev < 1 || n_dev > kMaxPeers) return fail(NB_ERR_INVALID, "nb_create_multi: 1..8 devices");
+    for (int i = 0; i < n_dev; ++i)
+        for (int j = 0; j < i; ++j)
+            if (devices[i] == devices[j]) return fail(NB_ERR_INVALID, "nb_create_multi: a device is listed twice");
+    if (n_dev == 1) return create_common(devices[0], 0, 1, out);
+    nb_group* g = new nb_group();
+    auto undo = [&]() {
+        for (nb_ctx* m : g->m) destroy_one(m);
+        delete g;
+    };
+    for (int i = 0; i < n_dev; ++i) {
+        nb_ctx* m = nullptr;
+        const int rc = create_common(devices[i], i, n_dev, &m);
+        if (rc != NB_OK) {
+            undo();
+            return rc;
+        }
+        g->m.push_back(m);
+    }
+    for (int i = 0; i < n_dev; ++i) {
+        cudaSetDevice(devices[i]);
+        for (int j = 0; j < n_dev; ++j) {
+            if (i == j) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, devices[i], devices[j]);
+            if (!can) {
+                undo();
+                return fail(NB_ERR_NO_DEVICE, "nb_create_multi: devices " + std::to_string(devices[i]) + " and " +
+                                                  std::to_string(devices[j]) + " cannot access each other's memory");
+            }
+            const cudaError_t e = cudaDeviceEnablePeerAccess(devices[j], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                undo();
+                return fail(NB_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+            }
+            cudaGetLastError();  // clear "already enabled"
+        }
+    }
+    for (nb_ctx* m : g->m) m->group = g;
+    *out = g->m[0];
+    return NB_OK;
+}
+
+extern "C" int nb_num_devices(nb_ctx* c) { return c ? (c->group ? (int)c->group->m.size() : 1) : -1; }
+
 extern "C" void nb_destroy(nb_ctx* c) {
     if (!c) return;
-    cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
-    cudaStreamSynchronize(c->comm_stream);
-    if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
-    free_bodies(c);
-    cudaFree(c->extent);
-    cudaFree(c->l2_scratch);
-    cudaFree(c->collide_scratch);
-    cudaFree(c->bh_scratch);
-    cudaFree(c->merge_scratch);
-    cudaFree(c->near_stats);
-    if (c->h_merge) cudaFreeHost(c->h_merge);
-    if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
-    cudaFree(c->totals);
-    cudaFreeHost(c->h_totals);
-    for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
-    cudaEventDestroy(c->ev_timer0);
-    cudaEventDestroy(c->ev_timer1);
-    cudaEventDestroy(c->ev_packed);
-    cudaEventDestroy(c->ev_gathered);
-    for (int g = 0; g < 2; ++g) {
-        cudaEventDestroy(c->ev_comm0[g]);
-        cudaEventDestroy(c->ev_comm1[g]);
+    if (c->group) {
+        nb_group* g = c->group;
+        for (nb_ctx* m : g->m) {
+            cudaSetDevice(m->device);
+            cudaStreamSynchronize(m->stream);
+        }
+        for (nb_ctx* m : g->m) destroy_one(m);
+        delete g;
+        return;
     }
-    cudaEventDestroy(c->ev_own0);
-    cudaEventDestroy(c->ev_own1);
-    cudaStreamDestroy(c->stream);
-    cudaStreamDestroy(c->comm_stream);
-    delete c;
+    destroy_one(c);
 }
 
 extern "C" int nb_set_config(nb_ctx* c, const nb_config* cfg) {
@@ -504,10 +577,12 @@ extern "C" int nb_set_config(nb_ctx* c, const nb_config* cfg) {
     if (cfg->integrator != NB_INTEGRATOR_EULER && cfg->integrator != NB_INTEGRATOR_VERLET)
         return fail(NB_ERR_INVALID, "nb_set_config: integrator must be 0 (Euler) or 1 (Verlet)");
     const bool repack = cfg->softening != c->cfg.softening || cfg->g != c->cfg.g;
-    c->cfg = *cfg;
-    if (repack) {  // accelerations depend on G and epsilon, and so does the drift prepared with them
-        c->acc_valid = false;
-        c->drop_speculation();
+    for (nb_ctx* s : Team(c)) {
+        s->cfg = *cfg;
+        if (repack) {  // accelerations depend on G and epsilon, and so does the drift prepared with them
+            s->acc_valid = false;
+            s->drop_speculation();
+        }
     }
     return NB_OK;
 }
@@ -522,8 +597,8 @@ extern "C" int64_t nb_num_bodies(nb_ctx* c) { return c ? c->n : -1; }
 
 extern "C" int nb_local_range(nb_ctx* c, int64_t* lo, int64_t* hi) {
     if (!c) return fail(NB_ERR_INVALID, "nb_local_range: null");
-    if (lo) *lo = c->lo;
-    if (hi) *hi = c->hi;
+    if (lo) *lo = c->group ? 0 : c->lo;  // one process holds every member's rows
+    if (hi) *hi = c->group ? c->n : c->hi;
     return NB_OK;
 }
 
@@ -550,10 +625,52 @@ extern "C" int nb_substep_plan(float dt, float max_substep, int32_t max_substeps
 // ---------------------------------------------------------------------------------------
 namespace {
 
+// Where member s's packs of generation parity `par` go: its own buffers first, then every peer's.
+PeerSet stream_out(nb_ctx* s, int par) {
+    PeerSet o;
+    memset(&o, 0, sizeof(o));
+    o.n = 0;
+    auto add = [&](nb_ctx* t) {
+        o.pk[o.n] = t->pk[par]; o.lo[o.n] = t->pk_lo[par]; o.hdr[o.n] = t->hdr[par]; o.extent[o.n] = t->extent;
+        o.n++;
+    };
+    add(s);
+    if (s->group)
+        for (nb_ctx* t : s->group->m)
+            if (t != s) add(t);
+    return o;
+}
+PeerSet diag_out(nb_ctx* s) {
+    PeerSet o = stream_out(s, 0);
+    int q = 0;
+    auto set = [&](nb_ctx* t) { o.pk[q] = t->dpk; o.lo[q] = t->dpk_lo; o.hdr[q] = t->dhdr; q++; };
+    set(s);
+    if (s->group)
+        for (nb_ctx* t : s->group->m)
+            if (t != s) set(t);
+    return o;
+}
+
+// Every member's stream waits for everything enqueued so far on every other member's stream.
+int team_barrier(nb_ctx* c) {
+    if (!c->group) return NB_OK;
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaEventRecord(s->ev_bar, s->stream));
+    }
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        for (nb_ctx* t : Team(c))
+            if (t != s) NB_CUDA(cudaStreamWaitEvent(s->stream, t->ev_bar, 0));
+    }
+    return NB_OK;
+}
+
 // All-gather generation `gen`'s j-stream slices (hi parts, residuals, group headers) in place and
 // max-reduce the rotating extent slot, on the comm stream, after everything enqueued so far on the main stream.
+// (NCCL-sharded contexts only: the members of a multi-GPU context wrote each other's buffers already.)
 int exchange_packed(nb_ctx* c, int gen, bool main_waits) {
-    if (c->world <= 1) return NB_OK;
+    if (c->world <= 1 || c->group) return NB_OK;
     NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
     NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
     const size_t rows = (size_t)c->tiles_per_rank * kTileBodies;
@@ -578,6 +695,28 @@ int exchange_packed(nb_ctx* c, int gen, bool main_waits) {
     return NB_OK;
 }
 
+// Multi-GPU context: every member announces that its packing launch is enqueued (ev_pub). Called once per
+// generation, AFTER every member's launches of the pass, so a member's wait for the previous generation
+// (consume_published) never picks up this newer record and serialises the team.
+int publish_all(nb_ctx* c) {
+    if (!c->group) return NB_OK;
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaEventRecord(s->ev_pub, s->stream));
+    }
+    return NB_OK;
+}
+// ... and member s's stream waits for every other member's announcement before it reads their rows.
+int consume_published(nb_ctx* s) {
+    if (s->group) {
+        for (nb_ctx* t : s->group->m)
+            if (t != s) NB_CUDA(cudaStreamWaitEvent(s->stream, t->ev_pub, 0));
+    } else if (s->world > 1) {
+        NB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_gathered, 0));
+    }
+    return NB_OK;
+}
+
 // Order this rank's stream rows along a Hilbert curve of the current positions (extent slot `slot` holds the
 // cube). Rows of other ranks keep whatever order their owner chose: only the owner reads `order`.
 int sort_stream(nb_ctx* c, int slot) {
@@ -597,19 +736,26 @@ int sort_stream(nb_ctx* c, int slot) {
     return NB_OK;
 }
 
-// Measure the extent of the current positions, open a new generation and pack it.
+// Measure the extent of the current positions, open a new generation and pack it (the whole team).
 int prepare_packed(nb_ctx* c) {
-    const StateView s = c->view();
-    c->gen += 1;
-    c->drop_speculation();
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        s->gen += 1;
+        s->drop_speculation();
+        NB_CUDA(cudaMemsetAsync(s->extent, 0, sizeof(unsigned int) * kExtentSlots, s->stream));
+    }
+    NB_TRY(team_barrier(c));  // nobody's peer atomics may land before the memset of the slot they hit
     const int g = c->gen;
-    NB_CUDA(cudaMemsetAsync(c->extent, 0, sizeof(unsigned int) * kExtentSlots, c->stream));
-    const long long n_local = c->hi - c->lo;
-    const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kStateThreads), 4 * c->sm_count);
-    extent_kernel<<<grid, kStateThreads, 0, c->stream>>>(s, c->extent, (g + kExtentSlots - 1) % kExtentSlots,
-                                                         g % kExtentSlots);
-    c->kernel_launches++;
-    if (c->world > 1) {
+    const int slot_cur = (g + kExtentSlots - 1) % kExtentSlots;
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kStateThreads), 4 * s->sm_count);
+        extent_kernel<<<grid, kStateThreads, 0, s->stream>>>(s->view(), stream_out(s, g & 1), slot_cur, g % kExtentSlots);
+        s->kernel_launches++;
+    }
+    if (c->world > 1 && !c->group) {
         // the pack below needs the GLOBAL extent: reduce it first (blocking the main stream)
         NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
         NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
@@ -618,23 +764,29 @@ int prepare_packed(nb_ctx* c) {
         NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     }
-    if (!c->order_valid || c->packs_since_sort >= c->resort_every) {
-        // a world of one group gains nothing from an ordering: it keeps upload order (and with it the lane
-        // pairing of the reference's mirror-symmetric three-body seed, whose pulls on the centre then cancel exactly)
-        if (c->n > kGroupBodies) NB_TRY(sort_stream(c, (g + kExtentSlots - 1) % kExtentSlots));
-        c->order_valid = true;
-        c->packs_since_sort = 0;
+    NB_TRY(team_barrier(c));  // every member's extent kernel has reached every copy of the slots
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        if (!s->order_valid || s->packs_since_sort >= s->resort_every) {
+            // a world of one group gains nothing from an ordering: it keeps upload order (and with it the lane
+            // pairing of the reference's mirror-symmetric three-body seed, whose pulls on the centre then cancel exactly)
+            if (s->n > kGroupBodies) NB_TRY(sort_stream(s, slot_cur));
+            s->order_valid = true;
+            s->packs_since_sort = 0;
+        }
+        if (n_local > 0) {
+            const long long groups = (s->tiles_per_rank * kTileBodies) / kGroupBodies;
+            pack_kernel<false><<<(unsigned int)groups, kGroupBodies, 0, s->stream>>>(
+                s->view(), s->order, stream_out(s, g & 1), s->live2[g & 1], s->extent, slot_cur, s->mass_exp, s->cfg.g,
+                s->cfg.softening);
+            s->kernel_launches++;
+        }
+        NB_CUDA(cudaGetLastError());
     }
-    if (n_local > 0) {
-        const long long groups = (c->tiles_per_rank * kTileBodies) / kGroupBodies;
-        pack_kernel<false><<<(unsigned int)groups, kGroupBodies, 0, c->stream>>>(
-            s, c->order, c->pk[g & 1], c->pk_lo[g & 1], c->hdr[g & 1], c->live2[g & 1], c->extent,
-            (g + kExtentSlots - 1) % kExtentSlots, c->mass_exp, c->cfg.g, c->cfg.softening);
-        c->kernel_launches++;
-    }
-    NB_CUDA(cudaGetLastError());
     NB_TRY(exchange_packed(c, g, true));
-    c->packed_valid = true;
+    NB_TRY(publish_all(c));
+    for (nb_ctx* s : team) s->packed_valid = true;
     return NB_OK;
 }
 
@@ -682,7 +834,7 @@ int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
         p.pk_cur = c->pk[c->gen & 1]; p.lo_cur = c->pk_lo[c->gen & 1]; p.hdr_cur = c->hdr[c->gen & 1];
         p.slot_cur = (c->gen + kExtentSlots - 1) % kExtentSlots; p.slot_nxt = c->gen % kExtentSlots;
     }
-    p.pk_next = c->pk[(c->gen + 1) & 1]; p.lo_next = c->pk_lo[(c->gen + 1) & 1]; p.hdr_next = c->hdr[(c->gen + 1) & 1];
+    p.out = stream_out(c, (c->gen + 1) & 1);
     p.extent = c->extent;
     p.part = c->part;
     p.tile_counter = c->tile_counter;
@@ -726,16 +878,26 @@ int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
 }
 
 // Own sources need no communication: in a sharded context a pass starts on them while the exchange of the
-// stream it reads may still be in flight, then finishes with the remote ones.
+// stream it reads may still be in flight, then finishes with the remote ones. The whole team, phase by phase.
 int launch_pass(nb_ctx* c, int mode, int kind, double dt) {
-    if (c->world > 1 && c->n_tiles > c->tiles_per_rank) {
-        if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_own0, c->stream));
-        NB_TRY(launch_force(c, 1, mode, kind, dt));
-        if (c->profile_comm) NB_CUDA(cudaEventRecord(c->ev_own1, c->stream));
-        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-        NB_TRY(launch_force(c, 2, mode, kind, dt));
-    } else {
-        NB_TRY(launch_force(c, 0, mode, kind, dt));
+    const Team team(c);
+    const bool split = c->world > 1 && c->n_tiles > c->tiles_per_rank;
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        if (split) {
+            if (s->profile_comm) NB_CUDA(cudaEventRecord(s->ev_own0, s->stream));
+            NB_TRY(launch_force(s, 1, mode, kind, dt));
+            if (s->profile_comm) NB_CUDA(cudaEventRecord(s->ev_own1, s->stream));
+        } else {
+            NB_TRY(launch_force(s, 0, mode, kind, dt));
+        }
+    }
+    if (split) {
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            NB_TRY(consume_published(s));
+            NB_TRY(launch_force(s, 2, mode, kind, dt));
+        }
     }
     return NB_OK;
 }
@@ -744,21 +906,29 @@ int launch_pass(nb_ctx* c, int mode, int kind, double dt) {
 // packed; kVerletKickDrift leaves it speculative (commit_drift()).
 int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
     if (!c->packed_valid) NB_TRY(prepare_packed(c));
+    const Team team(c);
     // a plain re-evaluation at the same positions through the same kernel reproduces Acceleration bit for
     // bit and leaves a prepared drift usable; anything else (another kernel variant, a move) does not
-    if (!(mode == kForceOnly && !pot && c->spec_kind == 0)) c->drop_speculation();
+    if (!(mode == kForceOnly && !pot && c->spec_kind == 0))
+        for (nb_ctx* s : team) s->drop_speculation();
     NB_TRY(launch_pass(c, mode, pot ? 1 : 0, dt));
-    c->force_evals++;
+    for (nb_ctx* s : team) s->force_evals++;
     if (mode == kEuler) {
-        c->gen += 1;
-        c->packs_since_sort++;
+        for (nb_ctx* s : team) {
+            s->gen += 1;
+            s->packs_since_sort++;
+            if (s->packs_since_sort >= s->resort_every) s->packed_valid = false;  // next pass re-sorts and re-packs
+        }
         NB_TRY(exchange_packed(c, c->gen, false));  // consumed by the next pass after its own-sources launch
-        if (c->packs_since_sort >= c->resort_every) c->packed_valid = false;  // next pass re-sorts and re-packs
+        NB_TRY(publish_all(c));
     } else if (mode == kVerletKickDrift) {
-        c->spec_valid = true;
-        c->spec_h = dt;
-        c->spec_kind = pot ? 1 : 0;
+        for (nb_ctx* s : team) {
+            s->spec_valid = true;
+            s->spec_h = dt;
+            s->spec_kind = pot ? 1 : 0;
+        }
         NB_TRY(exchange_packed(c, c->gen + 1, false));
+        NB_TRY(publish_all(c));
     }
     return NB_OK;
 }
@@ -766,12 +936,14 @@ int force_pass(nb_ctx* c, int mode, bool pot, double dt) {
 // The drift the last kick epilogue prepared becomes the state: Position <- shadow positions, generation + 1
 // (its j-stream, group headers, gather-filter flags and extent slot were written by that epilogue).
 void commit_drift(nb_ctx* c) {
-    c->x_sel ^= 1;
-    c->gen += 1;
-    c->packs_since_sort++;
-    c->spec_valid = false;
-    c->step_diag_valid = false;  // the fused potential described the positions before this drift
-    if (c->packs_since_sort >= c->resort_every) c->packed_valid = false;  // this pass re-sorts and re-packs
+    for (nb_ctx* s : Team(c)) {
+        s->x_sel ^= 1;
+        s->gen += 1;
+        s->packs_since_sort++;
+        s->spec_valid = false;
+        s->step_diag_valid = false;  // the fused potential described the positions before this drift
+        if (s->packs_since_sort >= s->resort_every) s->packed_valid = false;  // this pass re-sorts and re-packs
+    }
 }
 
 }  // namespace
@@ -783,12 +955,14 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
                       const uint8_t* pinned, int dim, const double* acc = nullptr) {
     if (!c) return fail(NB_ERR_INVALID, "nb_upload: null context");
     if (n < 0 || (n > 0 && (!pos || !vel || !mass))) return fail(NB_ERR_INVALID, "nb_upload: null array");
-    NB_CUDA(cudaSetDevice(c->device));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    c->dim = dim;
-    c->mass_exp = mass_exponent(mass, n);
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+    }
     // kernel specialisations (NB_FORCE_GENERIC=1 disables them): one common mass over every body that can
     // ever pass the gather filter, and z == 0 for reference-layout (2-D) uploads
+    const int mass_exp = mass_exponent(mass, n);
     float m0 = 0.f;
     bool uniform = n > 0, every = true;
     for (int64_t i = 0; i < n && uniform; ++i) {
@@ -800,40 +974,52 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
         if (m0 == 0.f) m0 = m;
         uniform = (m == m0);
     }
-    c->uniform_mass = uniform && m0 > 0.f && !c->force_generic;
-    c->diag_uniform_mass = c->uniform_mass && every;  // compute_diagnostics sums over ALL bodies
-    c->uniform_packed_mass = (double)m0 * pow2d(-c->mass_exp);
-    c->planar = dim == 2 && !c->force_generic;
-    NB_TRY(size_for(c, n));
-    c->acc_valid = false;
-    c->packed_valid = false; c->drop_speculation();
-    c->step_diag_valid = false;
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        s->dim = dim;
+        s->mass_exp = mass_exp;
+        s->uniform_mass = uniform && m0 > 0.f && !s->force_generic;
+        s->diag_uniform_mass = s->uniform_mass && every;  // compute_diagnostics sums over ALL bodies
+        s->uniform_packed_mass = (double)m0 * pow2d(-mass_exp);
+        s->planar = dim == 2 && !s->force_generic;
+        NB_TRY(size_for(s, n));
+        s->acc_valid = false;
+        s->packed_valid = false; s->drop_speculation();
+        s->step_diag_valid = false;
+    }
     if (n == 0) return NB_OK;
     // a rank only needs the FP64 state of its own targets: the other bodies reach it as FP32 sources
-    // through the all-gather of the packed stream (prepare_packed), so only rows [lo,hi) are copied
-    const long long rows = c->hi - c->lo;
-    if (rows > 0) {
-        const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)rows;
-        const size_t off = (size_t)c->lo * dim;
-        NB_TRY(ensure_staging(c, 3 * vec_bytes));
-        double* d_pos = static_cast<double*>(c->staging);
-        double* d_vel = d_pos + (size_t)dim * rows;
-        double* d_acc = d_vel + (size_t)dim * rows;
-        NB_CUDA(cudaMemcpyAsync(d_pos, pos + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-        NB_CUDA(cudaMemcpyAsync(d_vel, vel + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-        if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc + off, vec_bytes, cudaMemcpyHostToDevice, c->stream));
-        NB_CUDA(cudaMemcpyAsync(c->mass + c->lo, mass + c->lo, sizeof(float) * rows, cudaMemcpyHostToDevice, c->stream));
-        if (pinned)
-            NB_CUDA(cudaMemcpyAsync(c->pinned + c->lo, pinned + c->lo, (size_t)rows, cudaMemcpyHostToDevice, c->stream));
-        unpack_aos_kernel<<<blocks_for(rows, 256), 256, 0, c->stream>>>(d_pos, d_vel, acc ? d_acc : nullptr, dim, c->lo,
-                                                                       rows, c->view());
-        NB_CUDA(cudaGetLastError());
-        c->kernel_launches++;
+    // through the exchange of the packed stream (prepare_packed), so only rows [lo,hi) are copied
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long rows = s->hi - s->lo;
+        if (rows > 0) {
+            const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)rows;
+            const size_t off = (size_t)s->lo * dim;
+            NB_TRY(ensure_staging(s, 3 * vec_bytes));
+            double* d_pos = static_cast<double*>(s->staging);
+            double* d_vel = d_pos + (size_t)dim * rows;
+            double* d_acc = d_vel + (size_t)dim * rows;
+            NB_CUDA(cudaMemcpyAsync(d_pos, pos + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+            NB_CUDA(cudaMemcpyAsync(d_vel, vel + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+            if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+            NB_CUDA(cudaMemcpyAsync(s->mass + s->lo, mass + s->lo, sizeof(float) * rows, cudaMemcpyHostToDevice, s->stream));
+            if (pinned)
+                NB_CUDA(cudaMemcpyAsync(s->pinned + s->lo, pinned + s->lo, (size_t)rows, cudaMemcpyHostToDevice, s->stream));
+            unpack_aos_kernel<<<blocks_for(rows, 256), 256, 0, s->stream>>>(d_pos, d_vel, acc ? d_acc : nullptr, dim, s->lo,
+                                                                           rows, s->view());
+            NB_CUDA(cudaGetLastError());
+            s->kernel_launches++;
+        }
+        s->acc_valid = acc != nullptr;
     }
-    c->acc_valid = acc != nullptr;
-    NB_TRY(prepare_packed(c));
+    // The j-stream is packed by the first force pass that needs it (prepare_packed), not here: a frame that
+    // starts with a drift (Verlet with the caller's accelerations) would only throw this pack away.
     // the borrowed host arrays may be pageable: do not return while a copy could still read them
-    NB_CUDA(cudaStreamSynchronize(c->stream));
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+    }
     return NB_OK;
 }
 
@@ -853,21 +1039,27 @@ extern "C" int nb_upload_state(nb_ctx* c, int64_t n, int dim, const double* pos,
 
 static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int dim, double* acc_prev = nullptr) {
     if (!c) return fail(NB_ERR_INVALID, "nb_download: null context");
-    NB_CUDA(cudaSetDevice(c->device));
-    const long long n_local = c->hi - c->lo;
-    if (n_local <= 0) return NB_OK;
-    const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n_local;
-    NB_TRY(ensure_staging(c, 4 * vec_bytes));
+    const Team team(c);
     double* out[4] = {pos, vel, acc, acc_prev};
-    const StateView s = c->view();
-    for (int w = 0; w < 4; ++w) {
-        if (!out[w]) continue;
-        double* d = static_cast<double*>(c->staging) + (size_t)w * dim * n_local;
-        pack_aos_kernel<<<blocks_for(n_local, 256), 256, 0, c->stream>>>(s, w, dim, d);
-        c->kernel_launches++;
-        NB_CUDA(cudaMemcpyAsync(out[w] + (size_t)c->lo * dim, d, vec_bytes, cudaMemcpyDeviceToHost, c->stream));
+    for (nb_ctx* s : team) {  // every member fills its own rows of the caller's arrays
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        if (n_local <= 0) continue;
+        const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n_local;
+        NB_TRY(ensure_staging(s, 4 * vec_bytes));
+        const StateView v = s->view();
+        for (int w = 0; w < 4; ++w) {
+            if (!out[w]) continue;
+            double* d = static_cast<double*>(s->staging) + (size_t)w * dim * n_local;
+            pack_aos_kernel<<<blocks_for(n_local, 256), 256, 0, s->stream>>>(v, w, dim, d);
+            s->kernel_launches++;
+            NB_CUDA(cudaMemcpyAsync(out[w] + (size_t)s->lo * dim, d, vec_bytes, cudaMemcpyDeviceToHost, s->stream));
+        }
     }
-    NB_CUDA(cudaStreamSynchronize(c->stream));
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+    }
     return NB_OK;
 }
 
@@ -886,11 +1078,13 @@ extern "C" int nb_download_state(nb_ctx* c, int dim, double* pos, double* vel, d
 // bit-identical to the uninterrupted one carries it (scenarios.save_snapshot / load_snapshot).
 extern "C" int nb_stream_order(nb_ctx* c, int32_t* order, int64_t* generations_since_sort) {
     if (!c || !order) return fail(NB_ERR_INVALID, "nb_stream_order: null");
-    NB_CUDA(cudaSetDevice(c->device));
-    const long long n_local = c->hi - c->lo;
-    if (n_local > 0)
-        NB_CUDA(cudaMemcpyAsync(order + c->lo, c->order + c->lo, sizeof(int) * n_local, cudaMemcpyDeviceToHost, c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        if (n_local > 0)
+            NB_CUDA(cudaMemcpyAsync(order + s->lo, s->order + s->lo, sizeof(int) * n_local, cudaMemcpyDeviceToHost, s->stream));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+    }
     if (generations_since_sort) *generations_since_sort = c->packs_since_sort;
     return NB_OK;
 }
@@ -898,23 +1092,29 @@ extern "C" int nb_stream_order(nb_ctx* c, int32_t* order, int64_t* generations_s
 extern "C" int nb_set_stream_order(nb_ctx* c, const int32_t* order, int64_t generations_since_sort) {
     if (!c || !order) return fail(NB_ERR_INVALID, "nb_set_stream_order: null");
     if (generations_since_sort < 0) return fail(NB_ERR_INVALID, "nb_set_stream_order: negative age");
-    NB_CUDA(cudaSetDevice(c->device));
-    const long long n_local = c->hi - c->lo;
-    // the rows this context owns must be a permutation of themselves
-    std::vector<uint8_t> seen((size_t)std::max<long long>(n_local, 0), 0);
-    for (long long q = 0; q < n_local; ++q) {
-        const long long b = (long long)order[c->lo + q] - c->lo;
-        if (b < 0 || b >= n_local || seen[(size_t)b]) return fail(NB_ERR_INVALID, "nb_set_stream_order: not a permutation of the context's rows");
-        seen[(size_t)b] = 1;
+    for (nb_ctx* s : Team(c)) {
+        const long long n_local = s->hi - s->lo;
+        // the rows a context owns must be a permutation of themselves
+        std::vector<uint8_t> seen((size_t)std::max<long long>(n_local, 0), 0);
+        for (long long q = 0; q < n_local; ++q) {
+            const long long b = (long long)order[s->lo + q] - s->lo;
+            if (b < 0 || b >= n_local || seen[(size_t)b])
+                return fail(NB_ERR_INVALID, "nb_set_stream_order: not a permutation of the context's rows");
+            seen[(size_t)b] = 1;
+        }
     }
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    if (n_local > 0)
-        NB_CUDA(cudaMemcpyAsync(c->order + c->lo, order + c->lo, sizeof(int) * n_local, cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    c->order_valid = true;
-    c->packs_since_sort = generations_since_sort;
-    c->packed_valid = false; c->drop_speculation();
-    c->step_diag_valid = false;
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+        if (n_local > 0)
+            NB_CUDA(cudaMemcpyAsync(s->order + s->lo, order + s->lo, sizeof(int) * n_local, cudaMemcpyHostToDevice, s->stream));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+        s->order_valid = true;
+        s->packs_since_sort = generations_since_sort;
+        s->packed_valid = false; s->drop_speculation();
+        s->step_diag_valid = false;
+    }
     return NB_OK;
 }
 
@@ -1022,6 +1222,10 @@ static int exact_euler_move(nb_ctx* c, double h) {
 // ---------------------------------------------------------------------------------------
 // the hot path: compute_gravity / integrate / fused frames
 // ---------------------------------------------------------------------------------------
+static void set_acc_valid(nb_ctx* c, bool v) {
+    for (nb_ctx* s : Team(c)) s->acc_valid = v;
+}
+
 extern "C" int nb_compute_gravity(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_compute_gravity: null context");
     if (c->n == 0) return NB_OK;  // Physics.hpp:208
@@ -1029,7 +1233,7 @@ extern "C" int nb_compute_gravity(nb_ctx* c) {
     NB_TRY(check_solver(c));
     if (use_exact(c)) NB_TRY(exact_force(c));
     else NB_TRY(force_pass(c, kForceOnly, false, 0.0));
-    c->acc_valid = true;
+    set_acc_valid(c, true);
     return NB_OK;
 }
 
@@ -1037,19 +1241,21 @@ extern "C" int nb_compute_gravity(nb_ctx* c) {
 // Steady state is ONE launch per substep: the previous kick epilogue already drifted this substep into
 // the shadow positions and packed its j-stream (and, sharded, its all-gather is already in flight).
 static int verlet_substeps(nb_ctx* c, double h, long long n_sub, bool pot) {
-    const long long n_local = c->hi - c->lo;
     for (long long k = 0; k < n_sub; ++k) {
         if (c->spec_valid && c->spec_h == h && c->packed_valid) {
             commit_drift(c);
         } else {
             // first substep after an upload / edit / change of dt: stand-alone drift, new generation
-            c->drop_speculation();
-            if (n_local > 0) {
-                verlet_drift_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
-                                                                                                       0.5 * h * h);
-                c->kernel_launches++;
+            for (nb_ctx* s : Team(c)) {
+                NB_CUDA(cudaSetDevice(s->device));
+                const long long n_local = s->hi - s->lo;
+                if (n_local > 0) {
+                    verlet_drift_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                        s->view(), h, 0.5 * h * h);
+                    s->kernel_launches++;
+                }
+                s->packed_valid = false; s->drop_speculation();
             }
-            c->packed_valid = false; c->drop_speculation();
         }
         NB_TRY(force_pass(c, kVerletKickDrift, pot && (k + 1 == n_sub), h));
     }
@@ -1064,33 +1270,36 @@ extern "C" int nb_integrate(nb_ctx* c, float dt) {
     float dt_sub;
     const int n_steps = nb_substep_plan(dt, c->cfg.max_substep, c->cfg.max_substeps_per_frame, &dt_sub);
     const double h = (double)dt_sub;
-    const long long n_local = c->hi - c->lo;
     if (use_exact(c)) {
         if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
             for (int k = 0; k < n_steps; ++k) {
                 NB_TRY(exact_euler_move(c, h));
                 if (k + 1 < n_steps) NB_TRY(exact_force(c));  // Physics.hpp:292
             }
-            c->acc_valid = false;
+            set_acc_valid(c, false);
         } else {
             NB_TRY(exact_verlet(c, h, n_steps));
-            c->acc_valid = true;
+            set_acc_valid(c, true);
         }
         return NB_OK;
     }
     if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
         // kick/drift with the stored acceleration, then (gravity, kick/drift) per further substep
-        if (n_local > 0) {
-            euler_move_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(c->view(), h,
-                                                                                                 c->cfg.max_speed);
-            c->kernel_launches++;
+        for (nb_ctx* s : Team(c)) {
+            NB_CUDA(cudaSetDevice(s->device));
+            const long long n_local = s->hi - s->lo;
+            if (n_local > 0) {
+                euler_move_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(s->view(), h,
+                                                                                                     s->cfg.max_speed);
+                s->kernel_launches++;
+            }
+            s->packed_valid = false; s->drop_speculation();
         }
-        c->packed_valid = false; c->drop_speculation();
-        c->acc_valid = false;
+        set_acc_valid(c, false);
         for (int k = 1; k < n_steps; ++k) NB_TRY(force_pass(c, kEuler, false, h));
     } else {
         NB_TRY(verlet_substeps(c, h, n_steps, false));
-        c->acc_valid = true;  // Physics.hpp:324
+        set_acc_valid(c, true);  // Physics.hpp:324
     }
     NB_CUDA(cudaGetLastError());
     return NB_OK;
@@ -1118,7 +1327,7 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
         c->kernel_launches++;
         c->force_evals += total + first_force;
         c->interactions += (double)(total + first_force) * (double)c->n * (double)c->n;
-        c->acc_valid = verlet;  // Euler: Acceleration holds a(x) of the positions before the last move
+        set_acc_valid(c, verlet);  // Euler: Acceleration holds a(x) of the positions before the last move
         c->packed_valid = false; c->drop_speculation();
         c->step_diag_exact = pot;
         return NB_OK;
@@ -1129,10 +1338,10 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
                 NB_TRY(exact_force(c));
                 NB_TRY(exact_euler_move(c, h));
             }
-            c->acc_valid = false;
+            set_acc_valid(c, false);
         } else {
             if (!c->acc_valid) NB_TRY(exact_force(c));
-            c->acc_valid = true;
+            set_acc_valid(c, true);
             NB_TRY(exact_verlet(c, h, total));
         }
         c->step_diag_exact = pot;
@@ -1141,11 +1350,11 @@ static int step_impl(nb_ctx* c, float dt_eff, int64_t n_frames, bool pot) {
     if (c->cfg.integrator == NB_INTEGRATOR_EULER) {
         // frame = gravity system + n_steps x (kick/drift [+ gravity]): n_steps fused passes
         for (long long k = 0; k < total; ++k) NB_TRY(force_pass(c, kEuler, pot && (k + 1 == total), h));
-        c->acc_valid = false;  // Acceleration holds a(x) of the positions before the last move
+        set_acc_valid(c, false);  // Acceleration holds a(x) of the positions before the last move
     } else {
         // the gravity system's evaluation is only needed when Acceleration != a(x)
         if (!c->acc_valid) NB_TRY(force_pass(c, kForceOnly, false, 0.0));
-        c->acc_valid = true;
+        set_acc_valid(c, true);
         NB_TRY(verlet_substeps(c, h, total, pot));
     }
     return NB_OK;
@@ -1163,32 +1372,43 @@ namespace {
 
 // Sum `rows` per-CTA partial rows in fixed order on the device, combine the ranks' totals in
 // rank order on the host, and fill the reference's Diagnostics (Physics.hpp:163-176).
-int finish_diag(nb_ctx* c, long long rows, nb_diag* out) {
+int finish_diag(nb_ctx* c, nb_diag* out) {
     memset(out, 0, sizeof(*out));
-    double* h = c->h_totals;
-    for (int k = 0; k < kDiagValues; ++k) h[k] = 0.0;
-    if (rows > 0) {
-        sum_rows_kernel<<<1, 32, 0, c->stream>>>(c->diag_part, (int)rows, 10, kDiagValues, c->totals);
-        c->kernel_launches++;
-        NB_CUDA(cudaGetLastError());
-    } else {
-        NB_CUDA(cudaMemsetAsync(c->totals, 0, sizeof(double) * kDiagValues, c->stream));
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long rows = (s->hi - s->lo) > 0 ? s->step_diag_rows : 0;
+        for (int k = 0; k < kDiagValues; ++k) s->h_totals[k] = 0.0;
+        if (rows > 0) {
+            sum_rows_kernel<<<1, 32, 0, s->stream>>>(s->diag_part, (int)rows, 10, kDiagValues, s->totals);
+            s->kernel_launches++;
+            NB_CUDA(cudaGetLastError());
+        } else {
+            NB_CUDA(cudaMemsetAsync(s->totals, 0, sizeof(double) * kDiagValues, s->stream));
+        }
     }
     double t[kDiagValues];
-    if (c->world > 1) {
+    for (int k = 0; k < kDiagValues; ++k) t[k] = 0.0;
+    if (c->world > 1 && !c->group) {
         // every rank receives every rank's totals and adds them in rank order: bit-identical everywhere
+        double* h = c->h_totals;
         double* gathered = c->totals + 16;
         NB_NCCL(g_nccl.AllGather(c->totals, gathered, kDiagValues, kNcclFloat64, c->nccl_comm, c->stream));
         NB_CUDA(cudaMemcpyAsync(h, gathered, sizeof(double) * kDiagValues * c->world, cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        for (int k = 0; k < kDiagValues; ++k) {
-            t[k] = 0.0;
+        for (int k = 0; k < kDiagValues; ++k)
             for (int r = 0; r < c->world; ++r) t[k] += h[r * kDiagValues + k];
-        }
     } else {
-        NB_CUDA(cudaMemcpyAsync(h, c->totals, sizeof(double) * kDiagValues, cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
-        for (int k = 0; k < kDiagValues; ++k) t[k] = h[k];
+        // one process holds every member: read each member's totals and add them in member order
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            NB_CUDA(cudaMemcpyAsync(s->h_totals, s->totals, sizeof(double) * kDiagValues, cudaMemcpyDeviceToHost, s->stream));
+        }
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            NB_CUDA(cudaStreamSynchronize(s->stream));
+            for (int k = 0; k < kDiagValues; ++k) t[k] += s->h_totals[k];
+        }
     }
     const double M = t[8];
     bool ok = t[9] == 0.0;
@@ -1221,35 +1441,54 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
         out->ok = 1;
         return NB_OK;
     }
-    const StateView s = c->view();
-    const long long n_local = c->hi - c->lo;
     if (use_exact_precision(c)) {
         const long long rows = blocks_for(c->n, kDiagThreads);
-        diag_exact_kernel<<<(unsigned int)rows, kDiagThreads, 0, c->stream>>>(s, c->cfg.g, c->cfg.softening, c->diag_part);
+        diag_exact_kernel<<<(unsigned int)rows, kDiagThreads, 0, c->stream>>>(c->view(), c->cfg.g, c->cfg.softening,
+                                                                               c->diag_part);
         NB_CUDA(cudaGetLastError());
         c->kernel_launches++;
         c->step_diag_valid = false;
-        return finish_diag(c, rows, out);
+        c->step_diag_rows = rows;
+        return finish_diag(c, out);
     }
     // hot loop B (Physics.hpp:148-161) through the potential-only instantiation of the force kernel, over a
     // stream packed with this function's own rules (every body with a finite position, raw masses)
-    NB_CUDA(cudaMemsetAsync(c->extent + kDiagExtentSlot, 0, sizeof(unsigned int), c->stream));
-    if (n_local > 0) {
-        const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kDiagThreads), 4 * c->sm_count);
-        diag_extent_kernel<<<grid, kDiagThreads, 0, c->stream>>>(s.x[0], s.x[1], s.x[2], c->lo, c->hi, c->extent);
-        c->kernel_launches++;
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaMemsetAsync(s->extent + kDiagExtentSlot, 0, sizeof(unsigned int), s->stream));
     }
-    if (c->world > 1) {
+    NB_TRY(team_barrier(c));
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        if (n_local > 0) {
+            const StateView v = s->view();
+            const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n_local, kDiagThreads), 4 * s->sm_count);
+            diag_extent_kernel<<<grid, kDiagThreads, 0, s->stream>>>(v.x[0], v.x[1], v.x[2], s->lo, s->hi, diag_out(s));
+            s->kernel_launches++;
+        }
+    }
+    if (c->world > 1 && !c->group) {
         unsigned int* slot = c->extent + kDiagExtentSlot;
         NB_NCCL(g_nccl.AllReduce(slot, slot, 1, kNcclUint32, kNcclMax, c->nccl_comm, c->stream));
     }
-    if (n_local > 0) {
-        const long long groups = (c->tiles_per_rank * kTileBodies) / kGroupBodies;
-        pack_kernel<true><<<(unsigned int)groups, kGroupBodies, 0, c->stream>>>(
-            s, c->order, c->dpk, c->dpk_lo, c->dhdr, nullptr, c->extent, kDiagExtentSlot, c->mass_exp, 1.0, 0.f);
-        c->kernel_launches++;
+    NB_TRY(team_barrier(c));
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        if (!s->order_valid) {  // diagnostics right after an upload: order the stream now (the extent is known)
+            if (s->n > kGroupBodies) NB_TRY(sort_stream(s, kDiagExtentSlot));
+            s->order_valid = true;
+            s->packs_since_sort = 0;
+        }
+        if (s->hi - s->lo > 0) {
+            const long long groups = (s->tiles_per_rank * kTileBodies) / kGroupBodies;
+            pack_kernel<true><<<(unsigned int)groups, kGroupBodies, 0, s->stream>>>(
+                s->view(), s->order, diag_out(s), nullptr, s->extent, kDiagExtentSlot, s->mass_exp, 1.0, 0.f);
+            s->kernel_launches++;
+        }
     }
-    if (c->world > 1) {
+    if (c->world > 1 && !c->group) {
         const size_t rows_r = (size_t)c->tiles_per_rank * kTileBodies;
         const size_t count = rows_r * 4;
         const size_t hdr_count = rows_r / kGroupBodies * (sizeof(GroupHdr) / sizeof(float));
@@ -1261,10 +1500,15 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
         NB_NCCL(g_nccl.AllGather(hdb + (size_t)c->rank * hdr_count, hdb, hdr_count, kNcclFloat32, c->nccl_comm, c->stream));
         NB_NCCL(g_nccl.GroupEnd());
     }
-    NB_TRY(launch_force(c, 0, kDiagOnly, 2, 0.0));
-    NB_CUDA(cudaGetLastError());
-    c->step_diag_valid = false;  // diag_part was overwritten
-    return finish_diag(c, n_local > 0 ? c->step_diag_rows : 0, out);
+    NB_TRY(team_barrier(c));  // every member's rows are in every member's diagnostics stream
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_TRY(launch_force(s, 0, kDiagOnly, 2, 0.0));
+        NB_CUDA(cudaGetLastError());
+        s->step_diag_valid = false;  // diag_part was overwritten
+    }
+    NB_TRY(team_barrier(c));  // nobody re-packs a diagnostics stream a slower member is still reading
+    return finish_diag(c, out);
 }
 
 extern "C" int nb_step_diagnostics(nb_ctx* c, nb_diag* out) {
@@ -1276,50 +1520,73 @@ extern "C" int nb_step_diagnostics(nb_ctx* c, nb_diag* out) {
         return NB_OK;
     }
     if (c->step_diag_exact) return nb_compute_diagnostics(c, out);
-    if (!c->step_diag_valid && (c->hi - c->lo) > 0)
-        return fail(NB_ERR_INVALID, "nb_step_diagnostics: no nb_step_with_diagnostics since the last upload");
-    return finish_diag(c, (c->hi - c->lo) > 0 ? c->step_diag_rows : 0, out);
+    for (nb_ctx* s : Team(c))
+        if (!s->step_diag_valid && (s->hi - s->lo) > 0)
+            return fail(NB_ERR_INVALID, "nb_step_diagnostics: no nb_step_with_diagnostics since the last upload");
+    return finish_diag(c, out);
 }
 
 extern "C" int nb_zero_net_momentum(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_zero_net_momentum: null context");
     if (c->n == 0) return NB_OK;
-    NB_CUDA(cudaSetDevice(c->device));
-    const StateView s = c->view();
-    const long long n_local = c->hi - c->lo;
-    const int grid = (int)std::min<long long>(blocks_for(n_local, kStateThreads), std::min<long long>(c->diag_part_rows, 2 * c->sm_count));
-    if (n_local > 0) {
-        momentum_partial_kernel<<<grid, kStateThreads, 0, c->stream>>>(s, c->diag_part);
-        sum_rows_kernel<<<1, 32, 0, c->stream>>>(c->diag_part, grid, 4, 4, c->totals);
-        c->kernel_launches += 2;
-    } else {
-        NB_CUDA(cudaMemsetAsync(c->totals, 0, sizeof(double) * 4, c->stream));
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        const int grid = (int)std::min<long long>(blocks_for(n_local, kStateThreads),
+                                                  std::min<long long>(s->diag_part_rows, 2 * s->sm_count));
+        if (n_local > 0) {
+            momentum_partial_kernel<<<grid, kStateThreads, 0, s->stream>>>(s->view(), s->diag_part);
+            sum_rows_kernel<<<1, 32, 0, s->stream>>>(s->diag_part, grid, 4, 4, s->totals);
+            s->kernel_launches += 2;
+        } else {
+            NB_CUDA(cudaMemsetAsync(s->totals, 0, sizeof(double) * 4, s->stream));
+        }
     }
     if (c->world > 1) {
-        // rank-ordered sum on the device would need another kernel; totals are 4 doubles, so
-        // gather them and let every rank add in rank order on the host
-        double* gathered = c->totals + 16;
-        NB_NCCL(g_nccl.AllGather(c->totals, gathered, 4, kNcclFloat64, c->nccl_comm, c->stream));
-        NB_CUDA(cudaMemcpyAsync(c->h_totals, gathered, sizeof(double) * 4 * c->world, cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
+        // totals are 4 doubles: bring every rank's to the host and add them in rank order
         double t[4] = {0, 0, 0, 0};
-        for (int r = 0; r < c->world; ++r)
-            for (int k = 0; k < 4; ++k) t[k] += c->h_totals[r * 4 + k];
-        NB_CUDA(cudaMemcpyAsync(c->totals, t, sizeof(double) * 4, cudaMemcpyHostToDevice, c->stream));
-        NB_CUDA(cudaStreamSynchronize(c->stream));
+        if (!c->group) {
+            double* gathered = c->totals + 16;
+            NB_NCCL(g_nccl.AllGather(c->totals, gathered, 4, kNcclFloat64, c->nccl_comm, c->stream));
+            NB_CUDA(cudaMemcpyAsync(c->h_totals, gathered, sizeof(double) * 4 * c->world, cudaMemcpyDeviceToHost, c->stream));
+            NB_CUDA(cudaStreamSynchronize(c->stream));
+            for (int r = 0; r < c->world; ++r)
+                for (int k = 0; k < 4; ++k) t[k] += c->h_totals[r * 4 + k];
+        } else {
+            for (nb_ctx* s : team) {
+                NB_CUDA(cudaSetDevice(s->device));
+                NB_CUDA(cudaMemcpyAsync(s->h_totals, s->totals, sizeof(double) * 4, cudaMemcpyDeviceToHost, s->stream));
+            }
+            for (nb_ctx* s : team) {
+                NB_CUDA(cudaSetDevice(s->device));
+                NB_CUDA(cudaStreamSynchronize(s->stream));
+                for (int k = 0; k < 4; ++k) t[k] += s->h_totals[k];
+            }
+        }
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            for (int k = 0; k < 4; ++k) s->h_totals[32 + k] = t[k];  // pinned: stays valid for the async copy
+            NB_CUDA(cudaMemcpyAsync(s->totals, s->h_totals + 32, sizeof(double) * 4, cudaMemcpyHostToDevice, s->stream));
+            NB_CUDA(cudaStreamSynchronize(s->stream));
+        }
     }
-    if (n_local > 0) {
-        momentum_apply_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, c->stream>>>(s, c->totals);
-        c->kernel_launches++;
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        if (n_local > 0) {
+            momentum_apply_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(s->view(), s->totals);
+            s->kernel_launches++;
+        }
+        NB_CUDA(cudaGetLastError());
+        s->step_diag_valid = false;
+        // velocities changed: a prepared drift is void, and the gather filter (finite velocities, Physics.hpp:198-199)
+        // may now pass bodies it dropped (a pinned body's NaN velocity was just reset) -> re-pack and re-evaluate
+        // like the reference's next gravity system does
+        s->drop_speculation();
+        s->packed_valid = false;
+        s->acc_valid = false;
     }
-    NB_CUDA(cudaGetLastError());
-    c->step_diag_valid = false;
-    // velocities changed: a prepared drift is void, and the gather filter (finite velocities, Physics.hpp:198-199)
-    // may now pass bodies it dropped (a pinned body's NaN velocity was just reset) -> re-pack and re-evaluate
-    // like the reference's next gravity system does
-    c->drop_speculation();
-    c->packed_valid = false;
-    c->acc_valid = false;
     return NB_OK;
 }
 
@@ -1344,28 +1611,46 @@ extern "C" int nb_reset_scenario(nb_ctx* c) {
 // ---------------------------------------------------------------------------------------
 extern "C" int nb_synchronize(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_synchronize: null context");
-    NB_CUDA(cudaSetDevice(c->device));
-    NB_CUDA(cudaStreamSynchronize(c->stream));
-    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+        NB_CUDA(cudaStreamSynchronize(s->comm_stream));
+    }
     return NB_OK;
 }
 
 extern "C" int nb_timer_begin(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_timer_begin: null context");
-    NB_CUDA(cudaSetDevice(c->device));
-    NB_CUDA(cudaEventRecord(c->ev_timer0, c->stream));
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaEventRecord(s->ev_timer0, s->stream));
+    }
     return NB_OK;
 }
 
 extern "C" int nb_timer_end(nb_ctx* c, float* elapsed_ms) {
     if (!c || !elapsed_ms) return fail(NB_ERR_INVALID, "nb_timer_end: null");
-    NB_CUDA(cudaSetDevice(c->device));
-    // the exchange a step leaves in flight on the communication stream belongs to the step
-    if (c->world > 1) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-    NB_CUDA(cudaEventRecord(c->ev_timer1, c->stream));
-    NB_CUDA(cudaEventSynchronize(c->ev_timer1));
-    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
-    NB_CUDA(cudaEventElapsedTime(elapsed_ms, c->ev_timer0, c->ev_timer1));
+    // the exchange a step leaves in flight belongs to the step: an NCCL-sharded context waits for its
+    // all-gather, the members of a multi-GPU context for each other's packing launches
+    if (c->world > 1)
+        for (nb_ctx* s : Team(c)) {
+            NB_CUDA(cudaSetDevice(s->device));
+            NB_TRY(consume_published(s));
+        }
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaEventRecord(s->ev_timer1, s->stream));
+    }
+    float worst = 0.f;
+    for (nb_ctx* s : Team(c)) {  // device time, maximum over the members
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaEventSynchronize(s->ev_timer1));
+        NB_CUDA(cudaStreamSynchronize(s->comm_stream));
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, s->ev_timer0, s->ev_timer1));
+        worst = std::max(worst, ms);
+    }
+    *elapsed_ms = worst;
     return NB_OK;
 }
 
@@ -1381,10 +1666,12 @@ extern "C" int nb_device_info(nb_ctx* c, int* sm_count, int* cc_major, int* cc_m
 
 extern "C" int nb_flush_l2(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_flush_l2: null context");
-    NB_CUDA(cudaSetDevice(c->device));
     const size_t bytes = (size_t)256 << 20;
-    if (!c->l2_scratch) NB_CUDA(cudaMalloc(&c->l2_scratch, bytes));
-    NB_CUDA(cudaMemsetAsync(c->l2_scratch, 0x5a, bytes, c->stream));
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        if (!s->l2_scratch) NB_CUDA(cudaMalloc(&s->l2_scratch, bytes));
+        NB_CUDA(cudaMemsetAsync(s->l2_scratch, 0x5a, bytes, s->stream));
+    }
     return NB_OK;
 }
 
@@ -1401,9 +1688,15 @@ extern "C" int nb_free_pinned(void* p) {
 
 extern "C" int nb_counters(nb_ctx* c, int64_t* kernel_launches, int64_t* force_evals, double* interactions) {
     if (!c) return fail(NB_ERR_INVALID, "nb_counters: null context");
-    if (kernel_launches) *kernel_launches = c->kernel_launches;
+    long long k = 0;
+    double x = 0.0;
+    for (nb_ctx* s : Team(c)) {
+        k += s->kernel_launches;
+        x += s->interactions;
+    }
+    if (kernel_launches) *kernel_launches = k;
     if (force_evals) *force_evals = c->force_evals;
-    if (interactions) *interactions = c->interactions;
+    if (interactions) *interactions = x;
     return NB_OK;
 }
 
@@ -1453,8 +1746,10 @@ extern "C" int nb_overlap_profile(nb_ctx* c, int enable, float* ms4) {
 
 extern "C" int nb_profile_forces(nb_ctx* c, int enable) {
     if (!c) return fail(NB_ERR_INVALID, "nb_profile_forces: null context");
-    c->profile = enable != 0;
-    c->prof_used = 0;
+    for (nb_ctx* s : Team(c)) {
+        s->profile = enable != 0;
+        s->prof_used = 0;
+    }
     return NB_OK;
 }
 

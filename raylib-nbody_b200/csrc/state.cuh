@@ -21,8 +21,7 @@ struct StateView {
 };
 
 // max |coordinate| over bodies passing the gather filter -> extent slots `slot_a`, `slot_b`.
-__global__ void __launch_bounds__(kStateThreads) extent_kernel(StateView s, unsigned int* extent, int slot_a,
-                                                               int slot_b) {
+__global__ void __launch_bounds__(kStateThreads) extent_kernel(StateView s, PeerSet out, int slot_a, int slot_b) {
     __shared__ float red[kStateThreads / 32];
     float e = 0.f;
     for (long long i = s.lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < s.hi;
@@ -37,8 +36,10 @@ __global__ void __launch_bounds__(kStateThreads) extent_kernel(StateView s, unsi
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < kStateThreads / 32; ++w) e = fmaxf(e, red[w]);
-        atomicMax(&extent[slot_a], __float_as_uint(e));
-        atomicMax(&extent[slot_b], __float_as_uint(e));
+        for (int q = 0; q < out.n; ++q) {  // every device's copy (peer atomics over NVLink)
+            atomicMax(&out.extent[q][slot_a], __float_as_uint(e));
+            atomicMax(&out.extent[q][slot_b], __float_as_uint(e));
+        }
     }
 }
 
@@ -127,10 +128,9 @@ __global__ void __launch_bounds__(kStateThreads) iota_order_kernel(int* order, l
 // one CTA per group of kGroupBodies stream rows in [lo, row_cap). DIAG: the stream of the stand-alone
 // compute_diagnostics (Physics.hpp:117-161): every body with a finite position takes part with its raw mass.
 template <bool DIAG>
-__global__ void __launch_bounds__(kGroupBodies) pack_kernel(StateView s, const int* __restrict__ order, float* pk,
-                                                            float* lo_stream, GroupHdr* hdr, uint8_t* live_out,
-                                                            const unsigned int* extent, int slot, int mass_exp,
-                                                            double g, float softening) {
+__global__ void __launch_bounds__(kGroupBodies) pack_kernel(StateView s, const int* __restrict__ order, PeerSet out,
+                                                            uint8_t* live_out, const unsigned int* extent, int slot,
+                                                            int mass_exp, double g, float softening) {
     __shared__ float sbox[kGroupBodies / 32][6];
     const Scale sc = scale_for(extent[slot], mass_exp, g, softening);
     const double inv_mass = pow2d(-mass_exp);
@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(kGroupBodies) pack_kernel(StateView s, const i
             live_out[i] = attracts ? 1 : 0;
         }
     }
-    pack_group<kGroupBodies>(pk, lo_stream, hdr, row, x, m, attracts, sc.inv_len, inv_mass, sbox);
+    pack_group<kGroupBodies>(out, row, x, m, attracts, sc.inv_len, inv_mass, sbox);
 }
 
 // Velocity Verlet drift of the first substep of a call, Physics.hpp:297-304.

@@ -54,10 +54,10 @@ class Diagnostics:
                          self.com[0], self.com[1], self.total_mass])
 
 
-EXPORTS = ["nb_create", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
+EXPORTS = ["nb_create", "nb_create_multi", "nb_num_devices", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_stream_order", "nb_set_stream_order", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
-           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions",
+           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt",
            "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
@@ -82,6 +82,9 @@ def load_library(path=LIB_PATH):
     L.nb_num_bodies.restype = C.c_int64
     L.nb_num_bodies.argtypes = [C.c_void_p]
     L.nb_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    if hasattr(L, "nb_create_multi"):
+        L.nb_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        L.nb_num_devices.argtypes = [C.c_void_p]
     L.nb_create_sharded.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
     L.nb_destroy.argtypes = [C.c_void_p]
     L.nb_destroy.restype = None
@@ -101,6 +104,8 @@ def load_library(path=LIB_PATH):
     L.nb_count_overlaps.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.nb_resolve_collisions.argtypes = [C.c_void_p, _dp, _dp, C.POINTER(C.c_int64), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8),
                                         _dp, _dp, C.POINTER(C.c_float), C.POINTER(C.c_uint8), _dp, C.POINTER(C.c_int64), C.c_int64]
+    if hasattr(L, "nb_debug_cbrt"):
+        L.nb_debug_cbrt.argtypes = [C.c_void_p, _dp, _dp, C.c_int64]
     L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_default_config.argtypes = [C.POINTER(Config)]
@@ -188,11 +193,15 @@ def comm_unique_id():
 class Physics:
     """Device-resident world state with the reference's Physics entry points."""
 
-    def __init__(self, device=0, rank=0, world=1, unique_id=None):
+    def __init__(self, device=0, rank=0, world=1, unique_id=None, devices=None):
+        """devices=[0, 1, ...]: one single-process context over several GPUs (nb_create_multi)."""
         L = load_library()
         self._L = L
         self._h = C.c_void_p()
-        if world > 1:
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*devices)
+            _check(L.nb_create_multi(arr, len(devices), C.byref(self._h)))
+        elif world > 1:
             _check(L.nb_create_sharded(device, rank, world, unique_id, C.byref(self._h)))
         else:
             _check(L.nb_create(device, C.byref(self._h)))
@@ -351,6 +360,13 @@ class Physics:
                                                  log.ctypes.data_as(C.POINTER(C.c_int64)), log.shape[0]))
             return k.value, alive, changed, pos, vel, mass, pinned, rout, log[:k.value]
         return k.value, alive, changed, pos, vel, mass, pinned, rout
+
+    def debug_cbrt(self, x):
+        """Device restatement of glibc's cbrt (merge.cuh) on an array (test hook)."""
+        x = np.ascontiguousarray(x, np.float64)
+        out = np.zeros_like(x)
+        _check(self._L.nb_debug_cbrt(self._h, x.ctypes.data_as(_dp), out.ctypes.data_as(_dp), x.size))
+        return out
 
     def download_state(self):
         """(pos, vel, acc, acc_prev): the four DVec2 components of Components.hpp:10-21."""

@@ -113,8 +113,9 @@ def test_device_merge_pass_matches_oracle(pkg, oracle_lib, ob, name):
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,spread", [(20000, 4e8), (60000, 1.2e9)])
 def test_device_merge_pass_grid_broad_phase(pkg, oracle_lib, ob, n, spread):
-    """Above 2048 bodies the initial detection is the uniform-grid broad phase; merged bodies outgrow its cells,
-    which the per-merge rescans (all bodies) make irrelevant."""
+    """Above 2048 bodies the initial detection is the uniform-grid broad phase, and the scan after every merge
+    walks the same grid: merged bodies outgrow its cells and move off their initial positions, which the scan
+    covers by widening its reach (largest current radius + largest displacement so far)."""
     rng = np.random.default_rng(n)
     pos = (rng.standard_normal((n, 2)) * spread).astype(np.float32).astype(np.float64)
     vel = rng.standard_normal((n, 2)) * 1e3
@@ -146,3 +147,21 @@ def test_device_merge_pass_random_small_worlds(pkg, oracle_lib, ob):
         same_outcome(got[:8], want[:8])
         assert np.array_equal(got[8], want[8]), f"trial {trial}: merge order"
     ph.close()
+
+
+@pytest.mark.gpu
+def test_device_cbrt_is_glibc_bit_for_bit(pkg, oracle_lib):
+    """update_radius_from_mass (Collision.hpp:37-46) calls std::cbrt; glibc's is not correctly rounded, so the
+    device replay restates its algorithm operation by operation (merge.cuh::cbrt_glibc). Dense check against
+    this machine's libm: the merge code's argument range (3 m / (4 pi rho)) and the whole exponent range."""
+    rng = np.random.default_rng(99)
+    x = np.concatenate([
+        rng.uniform(1e-3, 1e30, 400000),
+        np.exp(rng.uniform(np.log(1e-300), np.log(1e300), 400000)),
+        3.0 * np.maximum(1.0, rng.uniform(1e20, 1e26, 200000).astype(np.float32).astype(np.float64)) / (4.0 * np.pi * 5510.0),
+        np.array([0.0, 1.0, 8.0, 27.0, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308, np.inf]),
+    ])
+    ph = pkg.Physics(0)
+    got = ph.debug_cbrt(x)
+    ph.close()
+    assert np.array_equal(got, oracle_lib.cbrt(x))   # (numpy's own cbrt is a different algorithm)

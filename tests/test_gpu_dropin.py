@@ -22,6 +22,23 @@ def test_flecs_dropin_matches_reference_systems():
     assert "DROPIN CHECK PASSED" in r.stdout and "FAIL" not in r.stdout
 
 
+@pytest.mark.gpu
+def test_flecs_dropin_on_several_gpus_in_one_process():
+    """Scenario F of the same binary: PhysicsB200::register_systems(w, devices) -> nb_create_multi. The reference's
+    systems are one process and one thread; so is this (no torchrun, no NCCL: peer-memory exchange)."""
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    if not os.path.exists(BIN):
+        pytest.skip("oracle/_ref/dropin_check not built (needs /root/reference at build time)")
+    env = dict(os.environ, NB_DROPIN_DEVICES=",".join(str(i) for i in range(min(n, 8))), NB_DROPIN_ONLY="F")
+    r = subprocess.run([BIN], capture_output=True, text=True, timeout=900, env=env)
+    print(r.stdout, r.stderr)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "GPUs in one process" in r.stdout and "FAIL" not in r.stdout
+
+
 def test_reference_side_binding_builds_and_links():
     """CPU: the binding compiles against the reference's headers and resolves every nb_* symbol
     from the product library (no compute call)."""

@@ -92,3 +92,40 @@ def test_sharded_matches_single_gpu(pkg, tmp_path, world, n, integ):
     assert np.abs(got["vel"] - v).max() <= 1e-11 * np.abs(v).max()
     assert np.allclose(got["fused"][:3], d_fused[:3], rtol=1e-11, atol=0)
     assert np.allclose(got["alone"][:3], d_alone[:3], rtol=1e-11, atol=0)
+
+
+# ---- one process, several GPUs (nb_create_multi): no torchrun, no NCCL -----------------------------
+@pytest.mark.parametrize("integ", [1, 0])
+@pytest.mark.parametrize("n_dev,n", [(2, 20000), (2, 700), (8, 9000), (3, 5000)])
+def test_single_process_multi_gpu_matches_single_gpu(pkg, n_dev, n, integ):
+    """The multi-GPU context a single-threaded host (the reference's flecs systems) can hold: members exchange
+    the packed stream through peer memory. Same partition as the sharded context, so the same check: it must
+    reproduce the single-GPU run (different summation grouping of the sources only), diagnostics included."""
+    if _n_gpus() < n_dev:
+        pytest.skip(f"needs {n_dev} GPUs")
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=17, dim=3)
+    eps = 3.844e8 / np.sqrt(n)
+    dt = 1e-3 * pkg.scenarios.crossing_time(n)
+    out = []
+    for devices in (None, list(range(n_dev))):
+        ph = pkg.Physics(0) if devices is None else pkg.Physics(devices=devices)
+        ph.set_precision(pkg.PRECISION_FP32)
+        ph.set_config(softening=eps, integrator=integ)
+        ph.upload(pos, vel, mass)
+        ph.zero_net_momentum()
+        ph.step(dt, 3)
+        for _ in range(2):                      # per-frame calls: the speculative-drift path
+            ph.step(dt, 1, diagnostics=True)
+        fused = ph.step_diagnostics().as_reference_array()
+        alone = ph.compute_diagnostics().as_reference_array()
+        state = ph.download()
+        lo, hi = ph.local_range()
+        assert (lo, hi) == (0, n)               # one process sees every row
+        ph.close()
+        out.append((state, fused, alone))
+    (s1, f1, a1), (s2, f2, a2) = out
+    scale = np.abs(s1[0]).max()
+    assert np.abs(s1[0] - s2[0]).max() / scale <= 1e-11
+    assert np.abs(s1[1] - s2[1]).max() / np.abs(s1[1]).max() <= 1e-9
+    assert np.abs(s1[2] - s2[2]).max() / np.abs(s1[2]).max() <= 1e-6
+    assert np.abs(f1 - f2)[:3].max() <= 1e-7 * abs(f1[2]) and np.abs(a1 - a2)[:3].max() <= 1e-7 * abs(a1[2])
