@@ -246,6 +246,32 @@ int nb_resolve_collisions(nb_ctx* ctx, const double* radius, const double* densi
                           uint8_t* alive, uint8_t* changed, double* pos_xy, double* vel_xy, float* mass,
                           uint8_t* pinned, double* radius_out, int64_t* merge_log, int64_t merge_log_cap);
 
+/* ---- scenario / checkpoint files (host-only; the reference keeps scenarios in memory, Scenario.hpp:14-128) ---- */
+
+/* The Config subset a Scenario carries to replay itself (Scenario.hpp:26-38), physics fields only. */
+typedef struct nb_scenario_config {
+    nb_config physics;      /* g, softening, max_speed, integrator, max_substep, max_substeps_per_frame */
+    int32_t bh_threshold;   /* Config.hpp:17 */
+    float bh_theta;         /* :18 */
+    int32_t use_fixed_dt;   /* :20 */
+    float fixed_dt;         /* :21 */
+    float time_scale;       /* :22 */
+} nb_scenario_config;
+#define NB_SCENARIO_HAS_ACC 1
+#define NB_SCENARIO_HAS_ACC_PREV 2
+#define NB_SCENARIO_HAS_ORDER 4
+int nb_scenario_default_config(nb_scenario_config* out);
+/* Bodies (BodySnapshot: pos, vel, mass, pinned; dim 2 = the reference's DVec2 layout) + the config subset, and
+ * optionally what a bit-exact resume needs: Acceleration, PrevAcceleration, the stream order and its age
+ * (nb_stream_order). One little-endian binary file, shared by scenarios.py and PhysicsB200.hpp. */
+int nb_scenario_write(const char* path, int64_t n, int dim, const double* pos, const double* vel, const double* acc,
+                      const double* acc_prev, const float* mass, const uint8_t* pinned, const nb_scenario_config* cfg,
+                      const int32_t* order, int64_t order_age, int64_t frame);
+int nb_scenario_read_header(const char* path, int64_t* n, int* dim, int* flags, nb_scenario_config* cfg,
+                            int64_t* order_age, int64_t* frame);
+int nb_scenario_read(const char* path, double* pos, double* vel, double* acc, double* acc_prev, float* mass,
+                     uint8_t* pinned, int32_t* order);
+
 /* Test hook: the device restatement of glibc's cbrt (update_radius_from_mass, Collision.hpp:37-46) on n values. */
 int nb_debug_cbrt(nb_ctx* ctx, const double* in, double* out, int64_t n);
 

@@ -29,6 +29,7 @@
 
 #include "components/Components.hpp"
 #include "core/Config.hpp"
+#include "core/Scenario.hpp"
 #include "systems/Collision.hpp"
 #include "systems/Physics.hpp"
 
@@ -352,6 +353,66 @@ public:
             dev.mirror = b;
             dev.frames++;
         });
+    }
+
+    // ---- scenarios on disk (the reference keeps them in memory only, src/core/Scenario.hpp:14-128) -----------
+    // A Scenario's bodies (pos, vel, mass, pinned) and the physics part of its config subset, in the C-ABI's
+    // ".nbs" format (nb_scenario_write), which scenarios.py reads and writes too. Render-only fields of a
+    // Scenario (name, tags, tint, meter_to_pixel, draw_*, trail_max, radius_scale) are UI state and stay out.
+    static void save_scenario(const Scenario& sc, const std::string& path) {
+        const size_t n = sc.bodies.size();
+        std::vector<double> pos(2 * n), vel(2 * n);
+        std::vector<float> mass(n);
+        std::vector<uint8_t> pinned(n);
+        for (size_t i = 0; i < n; ++i) {
+            pos[2 * i] = sc.bodies[i].pos.x; pos[2 * i + 1] = sc.bodies[i].pos.y;
+            vel[2 * i] = sc.bodies[i].vel.x; vel[2 * i + 1] = sc.bodies[i].vel.y;
+            mass[i] = sc.bodies[i].mass;
+            pinned[i] = sc.bodies[i].pinned ? 1 : 0;
+        }
+        nb_scenario_config c{};
+        c.physics.g = sc.g; c.physics.softening = sc.softening; c.physics.max_speed = sc.max_speed;
+        c.physics.integrator = sc.integrator; c.physics.max_substep = sc.max_substep;
+        c.physics.max_substeps_per_frame = sc.max_substeps_per_frame;
+        c.bh_threshold = sc.bh_threshold; c.bh_theta = sc.bh_theta;
+        c.use_fixed_dt = sc.use_fixed_dt ? 1 : 0; c.fixed_dt = sc.fixed_dt; c.time_scale = sc.time_scale;
+        check(nb_scenario_write(path.c_str(), (int64_t)n, 2, pos.data(), vel.data(), nullptr, nullptr, mass.data(),
+                                pinned.data(), &c, nullptr, 0, 0),
+              "nb_scenario_write");
+    }
+
+    // snapshot_from_world (Scenario.hpp:53-82) straight to a file.
+    static void save_scenario(const flecs::world& w, const std::string& path) {
+        save_scenario(snapshot_from_world(w, "", ""), path);
+    }
+
+    // A Scenario from a file; apply it with the reference's own apply_scenario_to_world (Scenario.hpp:107-128):
+    // the binding notices the new bodies at the next frame (mirror mismatch) and uploads them.
+    static Scenario load_scenario(const std::string& path) {
+        int64_t n = 0;
+        int dim = 0;
+        nb_scenario_config c{};
+        check(nb_scenario_read_header(path.c_str(), &n, &dim, nullptr, &c, nullptr, nullptr), "nb_scenario_read_header");
+        if (dim != 2) throw std::runtime_error("PhysicsB200::load_scenario: the reference's worlds are 2-D");
+        std::vector<double> pos(2 * (size_t)n), vel(2 * (size_t)n);
+        std::vector<float> mass((size_t)n);
+        std::vector<uint8_t> pinned((size_t)n);
+        check(nb_scenario_read(path.c_str(), pos.data(), vel.data(), nullptr, nullptr, mass.data(), pinned.data(), nullptr),
+              "nb_scenario_read");
+        Scenario sc{};
+        sc.bodies.resize((size_t)n);
+        for (size_t i = 0; i < (size_t)n; ++i) {
+            sc.bodies[i].pos = DVec2{pos[2 * i], pos[2 * i + 1]};
+            sc.bodies[i].vel = DVec2{vel[2 * i], vel[2 * i + 1]};
+            sc.bodies[i].mass = mass[i];
+            sc.bodies[i].pinned = pinned[i] != 0;
+        }
+        sc.g = c.physics.g; sc.softening = c.physics.softening; sc.max_speed = c.physics.max_speed;
+        sc.integrator = c.physics.integrator; sc.max_substep = c.physics.max_substep;
+        sc.max_substeps_per_frame = c.physics.max_substeps_per_frame;
+        sc.bh_threshold = c.bh_threshold; sc.bh_theta = c.bh_theta;
+        sc.use_fixed_dt = c.use_fixed_dt != 0; sc.fixed_dt = c.fixed_dt; sc.time_scale = c.time_scale;
+        return sc;
     }
 
     static void shutdown(const flecs::world& w) {

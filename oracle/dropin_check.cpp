@@ -359,6 +359,46 @@ int main() {
         expect(tb < tr, "the binding's default-settings frame is faster than the reference's");
         PhysicsB200::shutdown(wb);
     }
+    // ---- G: a scenario written to disk by the binding and applied to a fresh world (Scenario.hpp:53-128) ----------
+    {
+        flecs::world wa, wb;
+        make_config(wa, 1);
+        make_config(wb, 0);
+        PhysicsB200::register_systems(wa, 0);
+        PhysicsB200::register_systems(wb, 0);
+        add_disk(wa, 600, 77, 3.0e6f);
+        wa.get_mut<Config>()->time_scale = 2.0e4f;
+        {   // snapshot_from_world gathers bodies that carry a Tint (Scenario.hpp:77); not inside an iteration
+            std::vector<flecs::entity> es;
+            wa.each([&](flecs::entity e, const Position&) { es.push_back(e); });
+            for (auto& e : es) e.set<Tint>({WHITE});
+        }
+        const float dt = wa.get<Config>()->fixed_dt;
+        for (int f = 0; f < 4; ++f) wa.progress(dt);
+        const char* path = "/tmp/nb_dropin_scenario.nbs";
+        PhysicsB200::save_scenario(wa, path);
+        const nbody::Scenario sc = PhysicsB200::load_scenario(path);
+        nbody::apply_scenario_to_world(wb, sc);  // the reference's own apply: bodies + config subset
+        neutralise_collisions(wa);
+        neutralise_collisions(wb);
+        wb.get_mut<Config>()->bh_threshold = INT_MAX;
+        const Snapshot a0 = snap(wa), b0 = snap(wb);
+        std::printf("600-body scenario: binding -> .nbs file -> reference apply_scenario_to_world\n");
+        expect(sc.bodies.size() == 600 && bitwise(a0.pos, b0.pos) && bitwise(a0.vel, b0.vel),
+               "bodies round-trip bit for bit");
+        expect(wb.get<Config>()->integrator == 1 && wb.get<Config>()->softening == 3.0e6f &&
+                   wb.get<Config>()->time_scale == 2.0e4f,
+               "config subset applied (integrator, softening, time scale)");
+        for (int f = 0; f < 3; ++f) {
+            wa.progress(dt);
+            wb.progress(dt);
+        }
+        const Snapshot a1 = snap(wa), b1 = snap(wb);
+        // wb restarts with Acceleration = 0 like any applied scenario (Scenario.hpp:96): same frames from there
+        expect(max_rel(b1.pos, a1.pos) < 1e-9, "both worlds run on from the scenario");
+        PhysicsB200::shutdown(wa);
+        PhysicsB200::shutdown(wb);
+    }
     }  // scenarios A-E
     // ---- F: several GPUs behind the same flecs systems (nb_create_multi); devices from NB_DROPIN_DEVICES="0,1,.." -
     if (const char* list = std::getenv("NB_DROPIN_DEVICES")) {

@@ -131,6 +131,9 @@ struct StepParams {
     const uint8_t* live;        // gather filter of Physics.hpp:198-199 for generation `gen`, per body row
     uint8_t* live_next;         // ... for generation gen+1 (written together with the pack)
     const int* order;           // stream row -> body row, rows [i_lo, i_hi)
+    const double* tx_cur[3];    // FP64 positions of this rank's rows IN STREAM ORDER (generation `gen`): the targets' coordinates,
+                                // read coalesced by every (tile, segment) CTA instead of gathered through `order`
+    double* tx_next[3];         // ... of generation gen+1, written by the pack
     const float* pk_cur;        // pair-SoA j-stream being read (generation `gen`): hi parts
     const float* lo_cur;        // pair-SoA residuals {xl0,xl1,yl0,yl1,zl0,zl1,0,0}, read by the near path only
     const GroupHdr* hdr_cur;    // one per kGroupBodies stream rows

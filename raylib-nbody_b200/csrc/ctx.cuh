@@ -68,6 +68,8 @@ struct nb_ctx {
     float* mass = nullptr;
     uint8_t* pinned = nullptr;
     uint8_t* live2[2] = {nullptr, nullptr};  // gather-filter flags per generation parity (body rows)
+    double* tx[2] = {nullptr, nullptr}; // FP64 positions in stream order per generation, 3 * cap each (targets' coordinates)
+    double* dtx = nullptr;              // ... of the stand-alone diagnostics stream
     int* order = nullptr;               // stream row -> body row (Hilbert-curve order of this rank's rows)
     float* pk[2] = {nullptr, nullptr};  // pair-SoA j-stream generations: hi parts
     float* pk_lo[2] = {nullptr, nullptr};   // ... residuals (near path)

@@ -43,8 +43,9 @@ __device__ __forceinline__ float extent_of(const double (&x)[3], bool live) {
 // and half-extents; every row is stored as hi = float((x - c) * 2^-e), lo = float of the rest.
 // `sbox` is shared scratch of 6 floats per warp. All threads of the CTA must call this.
 template <int NT>
-__device__ __forceinline__ void pack_group(const PeerSet& out, long long row, const double (&x)[3], float m,
-                                           bool attracts, double inv_len, double inv_mass, float (*sbox)[6]) {
+__device__ __forceinline__ void pack_group(const PeerSet& out, double* const (&tx_out)[3], long long row,
+                                           const double (&x)[3], float m, bool attracts, double inv_len,
+                                           double inv_mass, float (*sbox)[6]) {
     static_assert(NT == kGroupBodies, "one thread per row of a group");
     const int tid = threadIdx.x;
     constexpr float kInf = __builtin_huge_valf();
@@ -108,6 +109,8 @@ __device__ __forceinline__ void pack_group(const PeerSet& out, long long row, co
     }
     g.reach = any ? kNearFactor * fmaxf(h[0], fmaxf(h[1], h[2])) : 0.f;
     g.pad[0] = g.pad[1] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) tx_out[k][row] = x[k];  // the row's FP64 position in stream order (this device only)
     const long long off = (row >> 1) * 8 + (row & 1);
     for (int q = 0; q < out.n; ++q) {  // this device, then every peer (stores over NVLink)
         float* rec = out.pk[q] + off;

@@ -31,7 +31,7 @@ namespace nb {
 
 constexpr int kUnrollPairs = NB_UNROLL_PAIRS;
 #ifndef NB_NEAR_UNROLL
-#define NB_NEAR_UNROLL 4
+#define NB_NEAR_UNROLL 2
 #endif
 constexpr int kNearUnroll = NB_NEAR_UNROLL;  // pair records per loop body of the near path
 

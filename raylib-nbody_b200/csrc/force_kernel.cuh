@@ -83,9 +83,8 @@ force_kernel(const __grid_constant__ StepParams p) {
     for (int r = 0; r < R; ++r) {
         const long long row = rbase + 32 * r;
         const bool ok = row < p.i_hi;
-        const long long body = ok ? (long long)p.order[row] : -1;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = ok ? __dmul_rn(p.x[k][body], cur.inv_len) : 1.0e300;
+        for (int k = 0; k < 3; ++k) tpos[k][li0 + 32 * r] = ok ? __dmul_rn(p.tx_cur[k][row], cur.inv_len) : 1.0e300;
         tg[r].reset();
         S[r][0] = S[r][1] = S[r][2] = S[r][3] = 0.0;
     }
@@ -173,7 +172,7 @@ force_kernel(const __grid_constant__ StepParams p) {
                 // statement would cost the hot loop its uniform-register addressing)
                 if (p.stats && (tid & 31) == 0) atomicAdd(&p.stats[1], 1ull);
 #ifndef NB_NEAR_RN
-#define NB_NEAR_RN 2
+#define NB_NEAR_RN 4  // targets per pass of the near path (4 + unroll 2 measured best: profiles/r02_time_variants.txt)
 #endif
                 constexpr int RN = R >= NB_NEAR_RN ? NB_NEAR_RN : (R >= 2 ? 2 : 1);
                 const float4* glo = reinterpret_cast<const float4*>(p.lo_cur) + j_group;
@@ -326,7 +325,7 @@ force_kernel(const __grid_constant__ StepParams p) {
             const double nx3[3] = {tpos[0][q * NT + tid], tpos[1][q * NT + tid], tpos[2][q * NT + tid]};
             const bool att = tatt[q * NT + tid] != 0;
             ext = fmaxf(ext, extent_of(nx3, att));
-            pack_group<NT>(p.out, row0 + (long long)q * NT + tid, nx3, tmass[q * NT + tid], att,
+            pack_group<NT>(p.out, p.tx_next, row0 + (long long)q * NT + tid, nx3, tmass[q * NT + tid], att,
                            nxt.inv_len, inv_mass, sbox);
         }
     }

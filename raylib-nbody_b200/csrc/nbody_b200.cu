@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <set>
 #include <string>
+#include <vector>
 
 #include "bh.cuh"
 #include "collide.cuh"
@@ -252,9 +253,11 @@ inline unsigned int blocks_for(long long n, int threads) { return (unsigned int)
 void free_bodies(nb_ctx* c) {
     cudaFree(c->state); cudaFree(c->mass); cudaFree(c->pinned); cudaFree(c->order);
     cudaFree(c->part); cudaFree(c->tile_counter); cudaFree(c->diag_part); cudaFree(c->staging);
-    cudaFree(c->dpk); cudaFree(c->dpk_lo); cudaFree(c->dhdr); cudaFree(c->sort_tmp);
+    cudaFree(c->dpk); cudaFree(c->dpk_lo); cudaFree(c->dhdr); cudaFree(c->sort_tmp); cudaFree(c->dtx);
+    c->dtx = nullptr;
     for (int g = 0; g < 2; ++g) {
-        cudaFree(c->live2[g]); cudaFree(c->pk[g]); cudaFree(c->pk_lo[g]); cudaFree(c->hdr[g]);
+        cudaFree(c->live2[g]); cudaFree(c->pk[g]); cudaFree(c->pk_lo[g]); cudaFree(c->hdr[g]); cudaFree(c->tx[g]);
+        c->tx[g] = nullptr;
         cudaFree(c->sort_keys[g]); cudaFree(c->sort_vals[g]);
         c->live2[g] = nullptr; c->pk[g] = c->pk_lo[g] = nullptr; c->hdr[g] = nullptr;
         c->sort_keys[g] = nullptr; c->sort_vals[g] = nullptr;
@@ -299,10 +302,12 @@ int size_for(nb_ctx* c, long long n) {
             NB_CUDA(cudaMalloc(&c->pk[g], sizeof(float) * 4 * rows));
             NB_CUDA(cudaMalloc(&c->pk_lo[g], sizeof(float) * 4 * rows));
             NB_CUDA(cudaMalloc(&c->hdr[g], sizeof(GroupHdr) * groups));
+            NB_CUDA(cudaMalloc(&c->tx[g], sizeof(double) * 3 * rows));
         }
         NB_CUDA(cudaMalloc(&c->dpk, sizeof(float) * 4 * rows));
         NB_CUDA(cudaMalloc(&c->dpk_lo, sizeof(float) * 4 * rows));
         NB_CUDA(cudaMalloc(&c->dhdr, sizeof(GroupHdr) * groups));
+        NB_CUDA(cudaMalloc(&c->dtx, sizeof(double) * 3 * rows));
         // Hilbert sort of this rank's rows (cub radix sort, double-buffered keys / values)
         const long long per_rank = c->tiles_per_rank * kTileBodies;
         for (int g = 0; g < 2; ++g) {
@@ -651,6 +656,12 @@ PeerSet diag_out(nb_ctx* s) {
     return o;
 }
 
+TxOut tx_out(double* base, long long cap) {
+    TxOut t;
+    for (int k = 0; k < 3; ++k) t.x[k] = base + (long long)k * cap;
+    return t;
+}
+
 // Every member's stream waits for everything enqueued so far on every other member's stream.
 int team_barrier(nb_ctx* c) {
     if (!c->group) return NB_OK;
@@ -778,8 +789,8 @@ int prepare_packed(nb_ctx* c) {
         if (n_local > 0) {
             const long long groups = (s->tiles_per_rank * kTileBodies) / kGroupBodies;
             pack_kernel<false><<<(unsigned int)groups, kGroupBodies, 0, s->stream>>>(
-                s->view(), s->order, stream_out(s, g & 1), s->live2[g & 1], s->extent, slot_cur, s->mass_exp, s->cfg.g,
-                s->cfg.softening);
+                s->view(), s->order, stream_out(s, g & 1), tx_out(s->tx[g & 1], s->cap), s->live2[g & 1], s->extent, slot_cur,
+                s->mass_exp, s->cfg.g, s->cfg.softening);
             s->kernel_launches++;
         }
         NB_CUDA(cudaGetLastError());
@@ -827,6 +838,10 @@ int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
     p.live = c->live2[c->gen & 1];
     p.live_next = c->live2[(c->gen + 1) & 1];
     p.order = c->order;
+    for (int k = 0; k < 3; ++k) {
+        p.tx_cur[k] = (kind == 2 ? c->dtx : c->tx[c->gen & 1]) + (long long)k * c->cap;
+        p.tx_next[k] = c->tx[(c->gen + 1) & 1] + (long long)k * c->cap;
+    }
     if (kind == 2) {
         p.pk_cur = c->dpk; p.lo_cur = c->dpk_lo; p.hdr_cur = c->dhdr;
         p.slot_cur = kDiagExtentSlot; p.slot_nxt = kDiagExtentSlot;
@@ -1484,7 +1499,8 @@ extern "C" int nb_compute_diagnostics(nb_ctx* c, nb_diag* out) {
         if (s->hi - s->lo > 0) {
             const long long groups = (s->tiles_per_rank * kTileBodies) / kGroupBodies;
             pack_kernel<true><<<(unsigned int)groups, kGroupBodies, 0, s->stream>>>(
-                s->view(), s->order, diag_out(s), nullptr, s->extent, kDiagExtentSlot, s->mass_exp, 1.0, 0.f);
+                s->view(), s->order, diag_out(s), tx_out(s->dtx, s->cap), nullptr, s->extent, kDiagExtentSlot, s->mass_exp, 1.0,
+                0.f);
             s->kernel_launches++;
         }
     }
@@ -1591,6 +1607,7 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
 }
 
 #include "host_collide.cuh"  // nb_count_overlaps, nb_resolve_collisions
+#include "host_scenario.cuh"  // nb_scenario_write / nb_scenario_read
 
 extern "C" int nb_reset_scenario(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_reset_scenario: null context");

@@ -127,10 +127,13 @@ __global__ void __launch_bounds__(kStateThreads) iota_order_kernel(int* order, l
 // FP64 state -> group-relative FP32 j-stream (hi, lo, group headers) + the gather filter's flags,
 // one CTA per group of kGroupBodies stream rows in [lo, row_cap). DIAG: the stream of the stand-alone
 // compute_diagnostics (Physics.hpp:117-161): every body with a finite position takes part with its raw mass.
+struct TxOut {
+    double* x[3];
+};
 template <bool DIAG>
 __global__ void __launch_bounds__(kGroupBodies) pack_kernel(StateView s, const int* __restrict__ order, PeerSet out,
-                                                            uint8_t* live_out, const unsigned int* extent, int slot,
-                                                            int mass_exp, double g, float softening) {
+                                                            TxOut tx, uint8_t* live_out, const unsigned int* extent,
+                                                            int slot, int mass_exp, double g, float softening) {
     __shared__ float sbox[kGroupBodies / 32][6];
     const Scale sc = scale_for(extent[slot], mass_exp, g, softening);
     const double inv_mass = pow2d(-mass_exp);
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(kGroupBodies) pack_kernel(StateView s, const i
             live_out[i] = attracts ? 1 : 0;
         }
     }
-    pack_group<kGroupBodies>(out, row, x, m, attracts, sc.inv_len, inv_mass, sbox);
+    pack_group<kGroupBodies>(out, tx.x, row, x, m, attracts, sc.inv_len, inv_mass, sbox);
 }
 
 // Velocity Verlet drift of the first substep of a call, Physics.hpp:297-304.

@@ -30,6 +30,12 @@ class Config(C.Structure):
                 ("integrator", C.c_int32), ("max_substep", C.c_float), ("max_substeps_per_frame", C.c_int32)]
 
 
+class ScenarioConfig(C.Structure):
+    """The Config subset a Scenario carries (Scenario.hpp:26-38), physics fields only (nb_scenario_config)."""
+    _fields_ = [("physics", Config), ("bh_threshold", C.c_int32), ("bh_theta", C.c_float), ("use_fixed_dt", C.c_int32),
+                ("fixed_dt", C.c_float), ("time_scale", C.c_float)]
+
+
 class _Diag(C.Structure):
     _fields_ = [("kinetic", C.c_double), ("potential", C.c_double), ("energy", C.c_double),
                 ("momentum", C.c_double * 3), ("com", C.c_double * 3), ("total_mass", C.c_double),
@@ -58,7 +64,7 @@ EXPORTS = ["nb_create", "nb_create_multi", "nb_num_devices", "nb_comm_unique_id"
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_stream_order", "nb_set_stream_order", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt",
-           "nb_substep_plan", "nb_reset_scenario", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
+           "nb_substep_plan", "nb_reset_scenario", "nb_scenario_default_config", "nb_scenario_write", "nb_scenario_read_header", "nb_scenario_read", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
@@ -125,6 +131,13 @@ def load_library(path=LIB_PATH):
     L.nb_zero_net_momentum.argtypes = [C.c_void_p]
     L.nb_substep_plan.argtypes = [C.c_float, C.c_float, C.c_int32, _fp]
     L.nb_reset_scenario.argtypes = [C.c_void_p]
+    if hasattr(L, "nb_scenario_write"):
+        L.nb_scenario_default_config.argtypes = [C.POINTER(ScenarioConfig)]
+        L.nb_scenario_write.argtypes = [C.c_char_p, C.c_int64, C.c_int, _dp, _dp, _dp, _dp, _fp, _bp, C.POINTER(ScenarioConfig),
+                                        C.POINTER(C.c_int32), C.c_int64, C.c_int64]
+        L.nb_scenario_read_header.argtypes = [C.c_char_p, C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                              C.POINTER(ScenarioConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.nb_scenario_read.argtypes = [C.c_char_p, _dp, _dp, _dp, _dp, _fp, _bp, C.POINTER(C.c_int32)]
     L.nb_synchronize.argtypes = [C.c_void_p]
     L.nb_timer_begin.argtypes = [C.c_void_p]
     L.nb_timer_end.argtypes = [C.c_void_p, _fp]
@@ -149,6 +162,51 @@ def default_config():
 def _check(status):
     if status != 0:
         raise NbodyError(status, (load_library().nb_last_error() or b"").decode())
+
+
+def scenario_write(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, config=None, stream_order=None, frame=0):
+    """One ".nbs" scenario / checkpoint file (nb_scenario_write): readable by every binding of the C-ABI."""
+    L = load_library()
+    pos = np.ascontiguousarray(pos, np.float64)
+    vel = np.ascontiguousarray(vel, np.float64)
+    mass = np.ascontiguousarray(mass, np.float32)
+    n, dim = pos.shape
+    cfg = ScenarioConfig()
+    _check(L.nb_scenario_default_config(C.byref(cfg)))
+    for k, v in (config or {}).items():
+        target = cfg.physics if hasattr(cfg.physics, k) else cfg
+        if not hasattr(target, k):
+            raise KeyError(f"not a scenario config field: {k}")
+        setattr(target, k, type(getattr(target, k))(v))
+    opt = lambda a, t: None if a is None else np.ascontiguousarray(a, t)
+    acc, acc_prev, pinned = opt(acc, np.float64), opt(acc_prev, np.float64), opt(pinned, np.uint8)
+    order = None if stream_order is None else np.ascontiguousarray(stream_order[0], np.int32)
+    ptr = lambda a, t: None if a is None else a.ctypes.data_as(t)
+    _check(L.nb_scenario_write(os.fsencode(path), n, dim, ptr(pos, _dp), ptr(vel, _dp), ptr(acc, _dp), ptr(acc_prev, _dp),
+                               ptr(mass, _fp), ptr(pinned, _bp), C.byref(cfg), ptr(order, C.POINTER(C.c_int32)),
+                               0 if stream_order is None else int(stream_order[1]), int(frame)))
+
+
+def scenario_read(path):
+    """-> dict(pos, vel, mass, pinned, acc|None, acc_prev|None, stream_order|None, config, frame) of a ".nbs" file."""
+    L = load_library()
+    n, dim, flags, age, frame = C.c_int64(), C.c_int(), C.c_int(), C.c_int64(), C.c_int64()
+    cfg = ScenarioConfig()
+    _check(L.nb_scenario_read_header(os.fsencode(path), C.byref(n), C.byref(dim), C.byref(flags), C.byref(cfg), C.byref(age),
+                                     C.byref(frame)))
+    n, dim, flags = n.value, dim.value, flags.value
+    pos, vel = np.zeros((n, dim)), np.zeros((n, dim))
+    mass, pinned = np.zeros(n, np.float32), np.zeros(n, np.uint8)
+    acc = np.zeros((n, dim)) if flags & 1 else None
+    acc_prev = np.zeros((n, dim)) if flags & 2 else None
+    order = np.zeros(n, np.int32) if flags & 4 else None
+    ptr = lambda a, t: None if a is None else a.ctypes.data_as(t)
+    _check(L.nb_scenario_read(os.fsencode(path), ptr(pos, _dp), ptr(vel, _dp), ptr(acc, _dp), ptr(acc_prev, _dp), ptr(mass, _fp),
+                              ptr(pinned, _bp), ptr(order, C.POINTER(C.c_int32))))
+    config = {k: getattr(cfg.physics, k) for k, _ in Config._fields_}
+    config.update({k: getattr(cfg, k) for k in ("bh_threshold", "bh_theta", "use_fixed_dt", "fixed_dt", "time_scale")})
+    return {"pos": pos, "vel": vel, "mass": mass, "pinned": pinned, "acc": acc, "acc_prev": acc_prev,
+            "stream_order": None if order is None else (order, age.value), "config": config, "frame": frame.value}
 
 
 def substep_plan(dt, max_substep, max_substeps_per_frame):

@@ -107,7 +107,16 @@ SNAPSHOT_CONFIG_KEYS = ("g", "softening", "max_speed", "integrator", "max_subste
 
 def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, config=None, frame=0, stream_order=None):
     """Bodies (Scenario::BodyData, Scenario.hpp:14-21) plus the physics Config fields. stream_order:
-    Physics.stream_order() of the run, for a resume that must be bit-identical (it fixes the summation order)."""
+    Physics.stream_order() of the run, for a resume that must be bit-identical (it fixes the summation order).
+    A path ending in ".nbs" is written in the C-ABI's own scenario format (nb_scenario_write), the one the
+    reference-side binding reads and writes too; anything else is a numpy .npz with the same content."""
+    if str(path).endswith(".nbs"):
+        from . import physics
+        for k in (config or {}):
+            if k not in SNAPSHOT_CONFIG_KEYS:
+                raise KeyError(f"not a physics Config field: {k}")
+        physics.scenario_write(path, pos, vel, mass, pinned, acc, acc_prev, config, stream_order, frame)
+        return
     n = len(mass)
     data = {"pos": np.asarray(pos, np.float64), "vel": np.asarray(vel, np.float64),
             "mass": np.asarray(mass, np.float32),
@@ -129,6 +138,12 @@ def save_snapshot(path, pos, vel, mass, pinned=None, acc=None, acc_prev=None, co
 
 def load_snapshot(path):
     """-> dict(pos, vel, mass, pinned, acc|None, acc_prev|None, stream_order|None, config, frame); floats round-trip exactly."""
+    if str(path).endswith(".nbs"):
+        from . import physics
+        d = physics.scenario_read(path)
+        d["config"] = {k: (int(v) if k in ("integrator", "max_substeps_per_frame") else float(v))
+                       for k, v in d["config"].items() if k in SNAPSHOT_CONFIG_KEYS}
+        return d
     z = np.load(path)
     cfg = {k: (int(z["cfg_" + k]) if k in ("integrator", "max_substeps_per_frame") else float(z["cfg_" + k]))
            for k in SNAPSHOT_CONFIG_KEYS if "cfg_" + k in z.files}

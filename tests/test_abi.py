@@ -100,3 +100,44 @@ def test_bench_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["unit"] == "interactions/s" and d["value"] > 0
     assert d["cpu_baseline"]["cores"] == 1 and d["cpu_baseline"]["kind"] in ("reference", "port")
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
+
+
+def test_scenario_file_round_trip_and_errors(pkg, tmp_path):
+    """The ".nbs" scenario / checkpoint format of the C-ABI (host-only, no GPU): floats and flags round-trip
+    exactly, optional arrays are optional, scenarios.save_snapshot/load_snapshot route ".nbs" paths through it,
+    and a bad file is a status code."""
+    rng = np.random.default_rng(3)
+    n = 257
+    pos, vel = rng.standard_normal((n, 2)) * 1e8, rng.standard_normal((n, 2)) * 1e3
+    acc, acc_prev = rng.standard_normal((n, 2)), rng.standard_normal((n, 2))
+    mass = rng.uniform(1e20, 1e25, n).astype(np.float32)
+    pinned = (rng.random(n) < 0.1).astype(np.uint8)
+    order = rng.permutation(n).astype(np.int32)
+    path = str(tmp_path / "world.nbs")
+    cfg = dict(g=6.5e-11, softening=123.5, max_speed=7.0, integrator=0, max_substep=0.25, max_substeps_per_frame=9,
+               bh_threshold=77, bh_theta=0.75, use_fixed_dt=1, fixed_dt=0.01, time_scale=3.0e4)
+    pkg.scenario_write(path, pos, vel, mass, pinned, acc, acc_prev, cfg, (order, 17), frame=42)
+    d = pkg.scenario_read(path)
+    for k, v in (("pos", pos), ("vel", vel), ("acc", acc), ("acc_prev", acc_prev), ("mass", mass), ("pinned", pinned)):
+        assert np.array_equal(d[k], v), k
+    assert np.array_equal(d["stream_order"][0], order) and d["stream_order"][1] == 17 and d["frame"] == 42
+    for k, v in cfg.items():
+        assert d["config"][k] == (np.float32(v) if isinstance(d["config"][k], float) and k != "g" else v), k
+    # optional arrays left out; 3-D
+    p3 = rng.standard_normal((5, 3))
+    pkg.scenario_write(path, p3, p3 * 2, mass[:5])
+    d = pkg.scenario_read(path)
+    assert d["acc"] is None and d["acc_prev"] is None and d["stream_order"] is None and not d["pinned"].any()
+    assert np.array_equal(d["pos"], p3) and d["config"]["integrator"] == 1 and d["config"]["bh_threshold"] == 100
+    # the package's snapshot helpers use the same file for ".nbs" paths
+    pkg.scenarios.save_snapshot(path, pos, vel, mass, pinned, acc=acc, config=dict(softening=4.0, integrator=1), frame=3,
+                                stream_order=(order, 2))
+    s = pkg.scenarios.load_snapshot(path)
+    assert np.array_equal(s["pos"], pos) and s["config"]["softening"] == 4.0 and s["frame"] == 3
+    assert s["acc_prev"] is None and s["stream_order"][1] == 2
+    with open(path, "wb") as f:
+        f.write(b"not a scenario")
+    with pytest.raises(pkg.NbodyError):
+        pkg.scenario_read(path)
+    with pytest.raises(pkg.NbodyError):
+        pkg.scenario_read(str(tmp_path / "missing.nbs"))
