@@ -275,6 +275,10 @@ int nb_scenario_read(const char* path, double* pos, double* vel, double* acc, do
 /* Test hook: the device restatement of glibc's cbrt (update_radius_from_mass, Collision.hpp:37-46) on n values. */
 int nb_debug_cbrt(nb_ctx* ctx, const double* in, double* out, int64_t n);
 
+/* Developer counters of the last nb_resolve_collisions that merged: values[4] = {merges, events popped and
+ * re-tested, bodies visited by the scans after the merges, initially overlapping pairs}. */
+int nb_merge_info(nb_ctx* ctx, int64_t* values);
+
 /* Substep plan of Physics.hpp:268-271 (float arithmetic). Host-only helper. */
 int nb_substep_plan(float dt, float max_substep, int32_t max_substeps_per_frame, float* dt_sub);
 

@@ -143,6 +143,7 @@ struct StepParams {
                                 // launches (local / remote sources), slots 1.. the source segments
     unsigned int* tile_counter; // [n_itiles] arrival counters (only nseg > 1)
     double* diag_part;          // [n_itiles][kDiagValues] per-CTA diagnostics partials
+    int* filter_flip;           // pinned host word (or null): set when a kick changes a body's gather-filter outcome
     unsigned long long* stats;  // null, or stats[1] counts the (warp, group) visits that took the near path
     long long n;                // bodies
     long long n_tiles;          // j-stream length in tiles of kTileBodies (padded with m = 0)

@@ -93,6 +93,7 @@ struct nb_ctx {
     long long diag_part_rows = 0;
     double* totals = nullptr;           // device scratch for fixed-order final sums (64 doubles)
     double* h_totals = nullptr;         // pinned host mirror
+    int* h_flip = nullptr;              // pinned, written by the kick epilogue: a body's gather-filter outcome changed
     void* l2_scratch = nullptr;         // 256 MiB, nb_flush_l2
     void* staging = nullptr;            // device staging for AoS uploads/downloads
     void* collide_scratch = nullptr;    // nb_count_overlaps: radii, grid arrays, scan temp
@@ -102,7 +103,7 @@ struct nb_ctx {
     size_t merge_bytes = 0;
     void* replay_scratch = nullptr;     // merge_replay_kernel: sorted keys, heap, snapshots, log
     size_t replay_bytes = 0;
-    long long merge_events = 0, merge_candidates = 0;  // of the last replay: events popped, bodies scanned
+    long long merge_last = 0, merge_initial = 0, merge_events = 0, merge_candidates = 0;  // of the last replay: events popped, bodies scanned
     long long merge_passes = 0;         // calls that found an overlap and replayed merges
     size_t staging_bytes = 0;
 
@@ -164,6 +165,15 @@ struct nb_ctx {
     double* pos_slot(int sel, int k) const { return sx((sel ? 12 : 0) + k); }
     uint8_t* live() const { return live2[gen & 1]; }
     void drop_speculation() { spec_valid = false; }
+    // after any synchronisation: a kick changed the gather filter -> the next frame re-packs and re-evaluates gravity
+    void absorb_filter_flip() {
+        if (h_flip && *h_flip) {
+            *h_flip = 0;
+            acc_valid = false;
+            packed_valid = false;
+            spec_valid = false;
+        }
+    }
     nb::StateView view() const {
         nb::StateView s;
         for (int k = 0; k < 3; ++k) {

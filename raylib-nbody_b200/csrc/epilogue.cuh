@@ -227,6 +227,10 @@ __device__ __forceinline__ void body_epilogue(const StepParams& p, long long i, 
             cap_speed(v, p.max_speed);
 #pragma unroll
             for (int k = 0; k < 3; ++k) p.v[k][i] = v[k];
+            // The reference's NEXT gravity system re-evaluates the gather filter with the kicked velocity
+            // (Physics.hpp:45-48,198-199); the fused path skips that pass as long as nothing changed. A kick
+            // that makes a velocity non-finite changes the filter: tell the host (it re-evaluates like the reference).
+            if (p.filter_flip && body_live(x, v, m) != live) *p.filter_flip = 1;
         }
         if (POT) diag_accumulate(dg, x, v, m, phi, p.g, live);
         if (mode == kVerletKick) return;

@@ -207,7 +207,6 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
 
     // ---- replay scratch (its own allocation: the pair sink above stays where it is) ------------------------
     unsigned long long heap_cap = (unsigned long long)std::max<long long>(8 * n, 1 << 20);
-    long long node_extra = std::max<long long>(4 * n, 1 << 16);  // re-binned survivors
     for (int attempt = 0;; ++attempt) {
         size_t cub_bytes = 0;
         NB_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, cub_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
@@ -220,12 +219,6 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
                      o_hits = take(4 * (size_t)n), o_pin = take((size_t)n), o_alive = take((size_t)n),
                      o_live = take((size_t)n), o_changed = take((size_t)n), o_log = take(16 * (size_t)std::max<int64_t>(merge_log_cap, 1)),
                      o_out = take(64);
-        // the hierarchical grid the scans walk (merge.cuh): list heads per level and cell, a node pool, each body's bin
-        const bool with_grid = used.g.cells[0] > 0;
-        const LevelGeom geom = with_grid ? level_geom(used.g) : LevelGeom{};
-        const long long node_cap = with_grid ? node_extra + n : 0;
-        const size_t o_heads = take(with_grid ? 4 * (size_t)geom.total : 0), o_nodes = take(8 * (size_t)node_cap),
-                     o_lvl = take(with_grid ? (size_t)n : 0), o_cell = take(with_grid ? 4 * (size_t)n : 0);
         if (off > c->replay_bytes) {
             NB_CUDA(cudaStreamSynchronize(c->stream));
             if (c->replay_scratch) cudaFree(c->replay_scratch);
@@ -251,15 +244,11 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
         double* d_rho = reinterpret_cast<double*>(rb + o_rho);
         mp.density = d_rho;
         const StateView sv = c->view();
+        mp.x_init = sv.x[0]; mp.y_init = sv.x[1];
         mp.initial = d_sorted; mp.n_initial = emitted;
         mp.heap = reinterpret_cast<unsigned long long*>(rb + o_heap); mp.heap_cap = heap_cap;
         mp.hits = reinterpret_cast<unsigned int*>(rb + o_hits);
-        mp.g = used.g;
-        mp.heads = reinterpret_cast<int*>(rb + o_heads);
-        mp.nodes = reinterpret_cast<int2*>(rb + o_nodes);
-        mp.node_cap = node_cap;
-        mp.lvl_of = reinterpret_cast<unsigned char*>(rb + o_lvl);
-        mp.cell_of = reinterpret_cast<int*>(rb + o_cell);
+        mp.g = used.g; mp.cell_start = used.cell_start; mp.sorted_idx = used.sorted_idx; mp.r_max = used.r_max;
         mp.merge_log = reinterpret_cast<long long*>(rb + o_log); mp.merge_log_cap = merge_log_cap;
         mp.out = reinterpret_cast<long long*>(rb + o_out);
         NB_CUDA(cudaMemcpyAsync(d_rho, density, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
@@ -267,24 +256,20 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
             NB_CUDA(cudaMemcpyAsync(mp.cr, radius, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
         merge_snapshot_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(sv.x[0], sv.x[1], sv.x[2], sv.v[0], sv.v[1], c->mass,
                                                                         c->pinned, n, mp);
-        if (with_grid) {
-            NB_CUDA(cudaMemsetAsync(mp.heads, 0xff, 4 * (size_t)geom.total, c->stream));  // -1: empty lists
-            merge_grid_build_kernel<<<blocks_for(n, 256), 256, 0, c->stream>>>(mp, geom);
-            c->kernel_launches++;
-        }
-        merge_replay_kernel<<<1, kMergeThreads, 0, c->stream>>>(mp, geom);
+        merge_replay_kernel<<<1, kMergeThreads, 0, c->stream>>>(mp);
         NB_CUDA(cudaGetLastError());
         c->kernel_launches += 2;
         long long out[4] = {0, 0, 0, 0};
         NB_CUDA(cudaMemcpyAsync(out, mp.out, sizeof(out), cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        if (out[1] != 0) {  // the event heap or the node pool overflowed: replay again with larger ones
+        if (out[1] != 0) {  // the event heap overflowed: replay again with a larger one
             if (attempt >= 6) return fail(NB_ERR_INVALID, "nb_resolve_collisions: event queue kept overflowing");
             heap_cap *= 4;
-            node_extra *= 4;
             continue;
         }
         const int64_t merges = out[0];
+        c->merge_last = out[0];
+        c->merge_initial = (long long)emitted;
         c->merge_events = out[2];
         c->merge_candidates = out[3];
         // ---- the outcome: dead bodies, survivors' new components, the merges in order ----------------------------
@@ -316,6 +301,17 @@ extern "C" int nb_resolve_collisions(nb_ctx* c, const double* radius, const doub
         c->merge_passes++;
         return NB_OK;
     }
+}
+
+// What the last nb_resolve_collisions replay did: {merges, events popped and re-tested, bodies visited by the
+// scans after the merges, initially overlapping pairs}.
+extern "C" int nb_merge_info(nb_ctx* c, int64_t* values) {
+    if (!c || !values) return fail(NB_ERR_INVALID, "nb_merge_info: null");
+    values[0] = c->merge_last;
+    values[1] = c->merge_events;
+    values[2] = c->merge_candidates;
+    values[3] = c->merge_initial;
+    return NB_OK;
 }
 
 // glibc's cbrt restated for the device (merge.cuh), for the test that pins it against libm.

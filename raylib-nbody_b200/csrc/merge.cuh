@@ -8,8 +8,8 @@
 //   * the pairs that overlap in the initial state (detected by the kernels of collide.cuh), sorted by
 //     key i*n + j (cub radix sort): consumed front to back;
 //   * after every merge, the pairs (survivor, k) whose current states overlap and whose key lies AHEAD of
-//     the event being processed: found by a neighbourhood scan of a hierarchical grid that follows the
-//     merges (LevelGrid below; all bodies when the world has no grid) and pushed on a binary min-heap.
+//     the event being processed: found by a neighbourhood scan of the uniform grid of the broad phase
+//     (or of all bodies when the world has no grid) and pushed on a binary min-heap.
 // Events are popped in key order and re-tested with the CURRENT snapshots; a pair that overlaps when the
 // reference would test it was detected either initially or by the scan after the last change of one of
 // its bodies, so the replay performs exactly the reference's merges, in its order (merge_log), with its
@@ -73,23 +73,22 @@ struct MergeParams {
     unsigned char* live;     // passes the input filter and is alive: what a scan may hit
     unsigned char* changed;
     const double* density;
+    const double* x_init; const double* y_init;  // the positions the grid was binned with
     // events
     const unsigned long long* initial;  // sorted keys of the initially overlapping pairs
     unsigned long long n_initial;
     unsigned long long* heap;
     unsigned long long heap_cap;
     unsigned int* hits;                 // scratch of one scan, n entries
-    // hierarchical grid over the CURRENT positions (g.cells[0] == 0: none, scan all bodies)
-    GridSpec g;                         // level 0 = the broad phase's grid (cell edge >= 2 x the largest initial radius)
-    int* heads;                         // per level, per cell: first node of the cell's list (-1: empty)
-    int2* nodes;                        // {body, next}; node i < n is body i's initial entry
-    long long node_cap;
-    unsigned char* lvl_of;              // where each living body is binned now: stale nodes are skipped
-    int* cell_of;
+    // grid of the broad phase (cells[0] == 0: none, scan all bodies)
+    GridSpec g;
+    const unsigned int* cell_start;
+    const unsigned int* sorted_idx;
+    double r_max;                       // largest radius at the start
     // results
     long long* merge_log;               // {survivor, absorbed} per merge, in order
     long long merge_log_cap;
-    long long* out;                     // [0] merges, [1] heap / node pool overflow, [2] events processed, [3] survivors re-binned
+    long long* out;                     // [0] merges, [1] heap overflow flag, [2] events processed, [3] scan candidates
 };
 
 __device__ __forceinline__ void heap_push(unsigned long long* h, unsigned long long& size, unsigned long long key) {
@@ -119,82 +118,24 @@ __device__ __forceinline__ unsigned long long heap_pop(unsigned long long* h, un
     return top;
 }
 
-// ---- LevelGrid: a hierarchy of uniform grids over the bodies' CURRENT positions ------------------------
-// Level L has cells of edge h0 * 2^L (h0: the broad phase's cell edge, >= 2 x the largest initial radius); a
-// body of radius r is binned at the lowest level whose cells are at least 2r wide, so at every level the
-// bodies a query can hit lie within (query radius + half a cell) of it. Merged bodies grow and move: the
-// survivor is re-binned (a new node in its new cell; the stale node is skipped because lvl_of/cell_of no
-// longer match), dead bodies are skipped through `live`. Cells are singly linked lists of nodes.
-constexpr int kMergeLevels = 16;
-
-struct LevelGeom {
-    int nx[kMergeLevels], ny[kMergeLevels];
-    long long off[kMergeLevels];  // first head of the level
-    long long total;
-};
-__host__ __device__ inline LevelGeom level_geom(const GridSpec& g) {
-    LevelGeom q;
-    long long off = 0;
-    for (int L = 0; L < kMergeLevels; ++L) {
-        q.nx[L] = ((g.cells[0] - 1) >> L) + 1;
-        q.ny[L] = ((g.cells[1] - 1) >> L) + 1;
-        q.off[L] = off;
-        off += (long long)q.nx[L] * q.ny[L];
-    }
-    q.total = off;
-    return q;
-}
-// lowest level whose cell edge covers a body of radius r (top level: catch-all)
-__device__ __forceinline__ int level_of_radius(const GridSpec& g, double r) {
-    const double need = 2.0 * r * (1.0 + 1e-9) * g.inv_h;  // in units of h0
-    int L = 0;
-    double edge = 1.0;
-    while (L < kMergeLevels - 1 && !(need <= edge)) {
-        edge *= 2.0;
-        ++L;
-    }
-    return L;
-}
-
-__global__ void __launch_bounds__(256) merge_grid_build_kernel(MergeParams p, LevelGeom q) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= p.n) return;
-    p.lvl_of[i] = 0;
-    p.cell_of[i] = -1;
-    if (!p.live[i]) return;
-    const int cx = grid_axis_cell(p.cx[i], p.g.origin[0], p.g.inv_h, p.g.cells[0]);
-    const int cy = grid_axis_cell(p.cy[i], p.g.origin[1], p.g.inv_h, p.g.cells[1]);
-    const int cell = cy * q.nx[0] + cx;  // every initial body fits level 0
-    p.cell_of[i] = cell;
-    p.nodes[i] = make_int2((int)i, atomicExch(&p.heads[q.off[0] + cell], (int)i));
-}
-
-__global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const MergeParams p, const LevelGeom q) {
-    __shared__ long long s_sv;            // survivor of the merge just applied
-    __shared__ double s_x, s_y, s_r;
+__global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const MergeParams p) {
+    __shared__ long long s_sv;            // survivor of the merge just applied, or -1: no scan needed
+    __shared__ double s_x, s_y, s_r, s_reach;
     __shared__ unsigned int s_nhits;
     __shared__ int s_done;
-    __shared__ int s_count[kMergeLevels];     // living bodies binned at each level
-    __shared__ double s_rmax[kMergeLevels];   // largest radius ever binned at each level
     const int tid = threadIdx.x;
     const unsigned long long un = (unsigned long long)p.n;
     const double pi = 3.141592653589793238462643383279502884;  // std::numbers::pi
-    const bool grid = p.g.cells[0] > 0;
 
     // thread 0's sequential state
     unsigned long long ptr = 0, heap_size = 0, key = 0, last_key = ~0ull;
-    long long cur_row = -1, merges = 0, events = 0, node_top = p.n;
+    long long cur_row = -1, merges = 0, events = 0, candidates = 0;
     bool row_alive = false, overflow = false;
-
-    if (tid < kMergeLevels) {
-        s_count[tid] = 0;  // levels >= 1 start empty and are counted exactly; level 0 is always scanned
-        s_rmax[tid] = 0.0;
-    }
-    __syncthreads();
-    if (tid == 0 && grid) s_rmax[0] = 0.5 / p.g.inv_h;  // every initial radius is <= h0 / 2
+    double r_max_now = p.r_max, max_shift = 0.0;
 
     for (;;) {
         if (tid == 0) {
+            s_sv = -1;
             s_done = 0;
             // ---- pop events until one merges (or none is left) ----------------------------------
             for (;;) {
@@ -243,39 +184,19 @@ __global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const Me
                 p.cr[sv] = rs;
                 p.changed[sv] = 1;
                 p.alive[dd] = 0;                                                                        // :124-125
-                if (p.live[dd]) {
-                    p.live[dd] = 0;
-                    if (grid && p.lvl_of[dd] > 0) s_count[p.lvl_of[dd]] -= 1;
-                }
+                p.live[dd] = 0;
                 if (merges < p.merge_log_cap) {
                     p.merge_log[2 * merges] = sv;
                     p.merge_log[2 * merges + 1] = dd;
                 }
                 ++merges;
-                // the survivor grew and moved: re-bin it (a dead row's body — it can still absorb, :76 — is in no list)
-                if (grid && p.live[sv]) {
-                    const int L = level_of_radius(p.g, rs);
-                    const int cx = grid_axis_cell(xx, p.g.origin[0], p.g.inv_h, p.g.cells[0]) >> L;
-                    const int cy = grid_axis_cell(xy, p.g.origin[1], p.g.inv_h, p.g.cells[1]) >> L;
-                    const int cell = cy * q.nx[L] + cx;
-                    s_rmax[L] = fmax(s_rmax[L], rs);
-                    if (L != (int)p.lvl_of[sv] || cell != p.cell_of[sv]) {
-                        if (node_top < p.node_cap) {
-                            int* head = &p.heads[q.off[L] + cell];
-                            p.nodes[node_top] = make_int2((int)sv, *head);
-                            *head = (int)node_top;
-                            ++node_top;
-                        } else {
-                            overflow = true;
-                        }
-                        if (p.lvl_of[sv] > 0) s_count[p.lvl_of[sv]] -= 1;
-                        if (L > 0) s_count[L] += 1;
-                        p.lvl_of[sv] = (unsigned char)L;
-                        p.cell_of[sv] = cell;
-                    }
-                }
+                // what the scan must cover: every living k whose CURRENT state can overlap the survivor's new
+                // one. The grid knows k's initial cell; k has moved by at most max_shift since (only survivors move).
+                r_max_now = fmax(r_max_now, rs);
+                max_shift = fmax(max_shift, fmax(fabs(xx - p.x_init[sv]), fabs(xy - p.y_init[sv])));
                 s_sv = sv;
                 s_x = xx; s_y = xy; s_r = rs;
+                s_reach = (rs + r_max_now + max_shift) * (1.0 + 1e-9);
                 s_nhits = 0;
                 break;
             }
@@ -286,6 +207,7 @@ __global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const Me
         const long long sv = s_sv;
         const double sx = s_x, sy = s_y, sr = s_r;
         auto test = [&](long long k) {
+            if (k == sv || !p.live[k]) return;
             // (x_B - x_A)^2 and r_A + r_B do not depend on which of the two is A: one form serves both orders
             const double dx = __dsub_rn(p.cx[k], sx);
             const double dy = __dsub_rn(p.cy[k], sy);
@@ -293,34 +215,27 @@ __global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const Me
             const double dist2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
             if (!(dist2 > __dmul_rn(rsum, rsum))) p.hits[atomicAdd(&s_nhits, 1u)] = (unsigned int)k;
         };
-        if (grid) {
-            for (int L = 0; L < kMergeLevels; ++L) {
-                if (L > 0 && s_count[L] <= 0) continue;
-                const double reach = (sr + s_rmax[L]) * (1.0 + 1e-9);
-                const int x_lo = grid_axis_cell(sx - reach, p.g.origin[0], p.g.inv_h, p.g.cells[0]) >> L;
-                const int x_hi = grid_axis_cell(sx + reach, p.g.origin[0], p.g.inv_h, p.g.cells[0]) >> L;
-                const int y_lo = grid_axis_cell(sy - reach, p.g.origin[1], p.g.inv_h, p.g.cells[1]) >> L;
-                const int y_hi = grid_axis_cell(sy + reach, p.g.origin[1], p.g.inv_h, p.g.cells[1]) >> L;
-                const int w = x_hi - x_lo + 1, cells = w * (y_hi - y_lo + 1);
-                for (int c = tid; c < cells; c += kMergeThreads) {
-                    const int cell = (y_lo + c / w) * q.nx[L] + x_lo + c % w;
-                    for (int node = p.heads[q.off[L] + cell]; node >= 0;) {
-                        const int2 nd = p.nodes[node];
-                        node = nd.y;
-                        const long long k = nd.x;
-                        if (k == sv || !p.live[k] || (int)p.lvl_of[k] != L || p.cell_of[k] != cell) continue;
-                        test(k);
-                    }
-                }
+        long long scanned = 0;
+        if (p.g.cells[0] > 0) {
+            const double reach = s_reach;
+            const int x_lo = grid_axis_cell(sx - reach, p.g.origin[0], p.g.inv_h, p.g.cells[0]);
+            const int x_hi = grid_axis_cell(sx + reach, p.g.origin[0], p.g.inv_h, p.g.cells[0]);
+            const int y_lo = grid_axis_cell(sy - reach, p.g.origin[1], p.g.inv_h, p.g.cells[1]);
+            const int y_hi = grid_axis_cell(sy + reach, p.g.origin[1], p.g.inv_h, p.g.cells[1]);
+            for (int qy = y_lo; qy <= y_hi; ++qy) {
+                const long long row = (long long)qy * p.g.cells[0];
+                const unsigned int k_lo = p.cell_start[row + x_lo], k_hi = p.cell_start[row + x_hi + 1];
+                for (unsigned int q = k_lo + tid; q < k_hi; q += kMergeThreads) test((long long)p.sorted_idx[q]);
+                scanned += k_hi - k_lo;
             }
         } else {
-            for (long long k = tid; k < p.n; k += kMergeThreads) {
-                if (k != sv && p.live[k]) test(k);
-            }
+            for (long long k = tid; k < p.n; k += kMergeThreads) test(k);
+            scanned = p.n;
         }
         __syncthreads();
         // ---- queue the hits that still lie ahead in the visiting order (thread 0) ----------------------
         if (tid == 0) {
+            candidates += scanned;
             const unsigned int nh = s_nhits;
             for (unsigned int h = 0; h < nh; ++h) {
                 const unsigned long long k = p.hits[h];
@@ -340,7 +255,7 @@ __global__ void __launch_bounds__(kMergeThreads, 1) merge_replay_kernel(const Me
         p.out[0] = merges;
         p.out[1] = overflow ? 1 : 0;
         p.out[2] = events;
-        p.out[3] = node_top - p.n;  // survivors re-binned
+        p.out[3] = candidates;
     }
 }
 

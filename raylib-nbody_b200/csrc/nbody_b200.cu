@@ -417,6 +417,7 @@ static void destroy_one(nb_ctx* c) {
     if (c->h_bh_ctl) cudaFreeHost(c->h_bh_ctl);
     cudaFree(c->totals);
     if (c->h_totals) cudaFreeHost(c->h_totals);
+    if (c->h_flip) cudaFreeHost(c->h_flip);
     for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
     cudaEvent_t evs[] = {c->ev_timer0, c->ev_timer1, c->ev_packed, c->ev_gathered, c->ev_comm0[0], c->ev_comm0[1],
                          c->ev_comm1[0], c->ev_comm1[1], c->ev_own0, c->ev_own1, c->ev_pub, c->ev_bar};
@@ -451,6 +452,8 @@ static int init_ctx(nb_ctx* c, int world) {
     const size_t totals_len = 48 + (size_t)kDiagValues * world + 16;
     NB_CUDA(cudaMalloc(&c->totals, sizeof(double) * totals_len));
     NB_CUDA(cudaMallocHost(&c->h_totals, sizeof(double) * totals_len));
+    NB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&c->h_flip), sizeof(int)));
+    *c->h_flip = 0;
     if (const char* v = getenv("NB_FORCE_R")) c->forced_r = atoi(v);
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
     if (const char* v = getenv("NB_RESORT_EVERY")) c->resort_every = std::max(1, atoi(v));
@@ -855,6 +858,7 @@ int launch_force(nb_ctx* c, int which, int mode, int kind, double dt) {
     p.tile_counter = c->tile_counter;
     p.diag_part = c->diag_part;
     p.stats = c->near_stats;
+    p.filter_flip = c->world == 1 ? c->h_flip : nullptr;  // single-GPU contexts (ranks would have to agree on it)
     p.n = c->n;
     p.n_tiles = c->n_tiles;
     p.i_lo = c->lo; p.i_hi = c->hi;
@@ -1074,6 +1078,7 @@ static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int di
     for (nb_ctx* s : team) {
         NB_CUDA(cudaSetDevice(s->device));
         NB_CUDA(cudaStreamSynchronize(s->stream));
+        s->absorb_filter_flip();
     }
     return NB_OK;
 }
@@ -1422,6 +1427,7 @@ int finish_diag(nb_ctx* c, nb_diag* out) {
         for (nb_ctx* s : team) {
             NB_CUDA(cudaSetDevice(s->device));
             NB_CUDA(cudaStreamSynchronize(s->stream));
+            s->absorb_filter_flip();
             for (int k = 0; k < kDiagValues; ++k) t[k] += s->h_totals[k];
         }
     }
@@ -1632,6 +1638,7 @@ extern "C" int nb_synchronize(nb_ctx* c) {
         NB_CUDA(cudaSetDevice(s->device));
         NB_CUDA(cudaStreamSynchronize(s->stream));
         NB_CUDA(cudaStreamSynchronize(s->comm_stream));
+        s->absorb_filter_flip();
     }
     return NB_OK;
 }

@@ -63,7 +63,7 @@ class Diagnostics:
 EXPORTS = ["nb_create", "nb_create_multi", "nb_num_devices", "nb_comm_unique_id", "nb_create_sharded", "nb_destroy", "nb_last_error", "nb_abi_version",
            "nb_default_config", "nb_set_config", "nb_get_config", "nb_set_precision", "nb_set_solver", "nb_get_solver", "nb_solver_info", "nb_solver_profile", "nb_upload", "nb_upload3", "nb_upload_state", "nb_download",
            "nb_download3", "nb_download_state", "nb_stream_order", "nb_set_stream_order", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
-           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt",
+           "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt", "nb_merge_info",
            "nb_substep_plan", "nb_reset_scenario", "nb_scenario_default_config", "nb_scenario_write", "nb_scenario_read_header", "nb_scenario_read", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
 
@@ -112,6 +112,8 @@ def load_library(path=LIB_PATH):
                                         _dp, _dp, C.POINTER(C.c_float), C.POINTER(C.c_uint8), _dp, C.POINTER(C.c_int64), C.c_int64]
     if hasattr(L, "nb_debug_cbrt"):
         L.nb_debug_cbrt.argtypes = [C.c_void_p, _dp, _dp, C.c_int64]
+    if hasattr(L, "nb_merge_info"):
+        L.nb_merge_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
     L.nb_set_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_get_config.argtypes = [C.c_void_p, C.POINTER(Config)]
     L.nb_default_config.argtypes = [C.POINTER(Config)]
@@ -418,6 +420,11 @@ class Physics:
                                                  log.ctypes.data_as(C.POINTER(C.c_int64)), log.shape[0]))
             return k.value, alive, changed, pos, vel, mass, pinned, rout, log[:k.value]
         return k.value, alive, changed, pos, vel, mass, pinned, rout
+
+    def merge_info(self):
+        v = (C.c_int64 * 4)()
+        _check(self._L.nb_merge_info(self._h, v))
+        return dict(merges=v[0], events=v[1], scanned=v[2], initial_pairs=v[3])
 
     def debug_cbrt(self, x):
         """Device restatement of glibc's cbrt (merge.cuh) on an array (test hook)."""

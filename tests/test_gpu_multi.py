@@ -86,12 +86,14 @@ def test_sharded_matches_single_gpu(pkg, tmp_path, world, n, integ):
     d_alone = ph.compute_diagnostics().as_reference_array()
     p, v, a = ph.download()
     ph.close()
-    # same FP32 pair terms; only the FP64 order of combining source ranges differs
-    assert np.abs(got["acc"] - a).max() <= 1e-11 * np.abs(a).max()
-    assert np.abs(got["pos"] - p).max() <= 1e-12 * np.abs(p).max()
-    assert np.abs(got["vel"] - v).max() <= 1e-11 * np.abs(v).max()
-    assert np.allclose(got["fused"][:3], d_fused[:3], rtol=1e-11, atol=0)
-    assert np.allclose(got["alone"][:3], d_alone[:3], rtol=1e-11, atol=0)
+    # Every rank orders its own slice of the stream along its own Hilbert curve, so the sharded run groups the FP32
+    # pair terms differently from the single-GPU run (round 1 streamed in index order on every rank and agreed to
+    # 1e-11): two valid FP32 evaluations of the same sums, a few 1e-7 of the largest acceleration apart.
+    assert np.abs(got["acc"] - a).max() <= 1e-6 * np.abs(a).max()
+    assert np.abs(got["pos"] - p).max() <= 1e-11 * np.abs(p).max()
+    assert np.abs(got["vel"] - v).max() <= 1e-9 * np.abs(v).max()
+    assert np.allclose(got["fused"][:3], d_fused[:3], rtol=1e-7, atol=0)
+    assert np.allclose(got["alone"][:3], d_alone[:3], rtol=1e-7, atol=0)
 
 
 # ---- one process, several GPUs (nb_create_multi): no torchrun, no NCCL -----------------------------

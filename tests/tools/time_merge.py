@@ -25,7 +25,8 @@ def main():
         t0 = time.perf_counter()
         k, alive, changed, *_ = ph.resolve_collisions(radius, density)
         t_gpu = time.perf_counter() - t0
-        line = f"n={n} radius x{scale}: {k} merges, {int((alive == 0).sum())} bodies destructed; device pass {t_gpu*1e3:.2f} ms"
+        info = ph.merge_info()
+        line = f"n={n} radius x{scale}: {info['initial_pairs']} pairs overlap initially, {info['events']} events re-tested, {info['scanned']} bodies scanned; {k} merges, {int((alive == 0).sum())} bodies destructed; device pass {t_gpu*1e3:.2f} ms"
         if cpu:
             t0 = time.perf_counter()
             if ob.have_reference():
