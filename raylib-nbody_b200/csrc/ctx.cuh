@@ -60,6 +60,7 @@ struct nb_ctx {
     // ---- bodies ----
     long long n = 0;          // all bodies
     long long cap = 0;        // allocated rows
+    long long n_sized = -1;   // body count the buffers were last initialised for
     long long lo = 0, hi = 0; // rows owned by this rank
     long long n_tiles = 0;    // j-stream tiles (padded to world * tiles_per_rank)
     long long tiles_per_rank = 0;
