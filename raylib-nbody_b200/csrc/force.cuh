@@ -33,7 +33,8 @@ constexpr int kUnrollPairs = NB_UNROLL_PAIRS;
 #ifndef NB_NEAR_UNROLL
 #define NB_NEAR_UNROLL 2
 #endif
-constexpr int kNearUnroll = NB_NEAR_UNROLL;  // pair records per loop body of the near path
+constexpr int kNearUnroll = NB_NEAR_UNROLL;  // pair records per loop body of the near path at 3-4 targets per pass
+                                             // (x2 at two targets, x4 at one: small worlds run R = 1 and are all "near")
 
 // float -> double of a chunk sum. F2F.F64.F32 runs on the XU pipe next to the kernel's MUFU.RSQ stream
 // (one conversion costs as much XU time as a MUFU); NB_INT_FLUSH builds the double from the float's bits
@@ -196,14 +197,14 @@ __device__ __forceinline__ void chunk_interact(Target<POT, EQM, D2, PONLY> (&t)[
 // residual records in global memory (L2/L1-resident; every lane reads the same address). nl[q][k]:
 // {-lo_i, -lo_i} of target r0+q, axis k. Partially unrolled: this path runs for the handful of groups
 // whose bounding box a warp's targets touch, and must not cost the hot loop registers.
-template <int RN, int R, bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY, int RS>
+template <int RN, int R, bool POT, bool MASK, int CH, bool EQM, bool D2, bool PONLY, int RS, int NU = 1>
 __device__ __forceinline__ void chunk_interact_near(Target<POT, EQM, D2, PONLY> (&t)[R], int r0,
                                                     const float4* __restrict__ rec,
                                                     const float4* __restrict__ lo_rec, const f2 (&nl)[RN][3],
                                                     float eps2, long long j_first, long long row0) {
     const f2 e2 = f2_make(eps2, eps2);
     const f2 zero = f2_make(0.f, 0.f);
-#pragma unroll kNearUnroll
+#pragma unroll (NU * (RN >= 3 ? kNearUnroll : (RN == 2 ? 2 * kNearUnroll : 4 * kNearUnroll)))
     for (int u = 0; u < CH / 2; ++u) {
         f2 xj, yj, zj, mj, xl, yl, zl, unused;
         load_pair<!D2, !EQM>(rec + 2 * u, xj, yj, zj, mj);

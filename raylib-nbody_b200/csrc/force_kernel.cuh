@@ -34,8 +34,11 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// NU: unroll multiplier of the near path. 1 for the large-N variants (the near path is rare there and its code
+// must not disturb the hot loop's schedule); 4 for the "mid" variants the planner picks when the world has few
+// source tiles and a large share of the (warp, group) visits is near.
 template <int NT, int R, bool POT, int MINB, int CH = kFlushChunk, bool EQM = false, bool D2 = false,
-          bool PONLY = false>
+          bool PONLY = false, int NU = 1>
 __global__ void __launch_bounds__(NT, MINB)
 force_kernel(const __grid_constant__ StepParams p) {
     static_assert(NT == kGroupBodies, "a target slice r of a CTA is exactly one group of the next generation");
@@ -197,10 +200,10 @@ force_kernel(const __grid_constant__ StepParams p) {
                             }
                         }
                         if (diag_tile)
-                            chunk_interact_near<RN, R, POT, true, CH, EQM, D2, PONLY, 32>(tg, r0, rec, lrec, nl, cur.eps2,
+                            chunk_interact_near<RN, R, POT, true, CH, EQM, D2, PONLY, 32, NU>(tg, r0, rec, lrec, nl, cur.eps2,
                                                                                           j_first, rbase);
                         else
-                            chunk_interact_near<RN, R, POT, false, CH, EQM, D2, PONLY, 32>(tg, r0, rec, lrec, nl, cur.eps2,
+                            chunk_interact_near<RN, R, POT, false, CH, EQM, D2, PONLY, 32, NU>(tg, r0, rec, lrec, nl, cur.eps2,
                                                                                            j_first, rbase);
                     }
                     if (R % RN) {  // R = 3: the odd target on its own
@@ -215,10 +218,10 @@ force_kernel(const __grid_constant__ StepParams p) {
                             nl1[0][k] = f2_make(fl, fl);
                         }
                         if (diag_tile)
-                            chunk_interact_near<1, R, POT, true, CH, EQM, D2, PONLY, 32>(tg, rl, rec, lrec, nl1, cur.eps2,
+                            chunk_interact_near<1, R, POT, true, CH, EQM, D2, PONLY, 32, NU>(tg, rl, rec, lrec, nl1, cur.eps2,
                                                                                          j_first, rbase);
                         else
-                            chunk_interact_near<1, R, POT, false, CH, EQM, D2, PONLY, 32>(tg, rl, rec, lrec, nl1, cur.eps2,
+                            chunk_interact_near<1, R, POT, false, CH, EQM, D2, PONLY, 32, NU>(tg, rl, rec, lrec, nl1, cur.eps2,
                                                                                           j_first, rbase);
                     }
 #pragma unroll

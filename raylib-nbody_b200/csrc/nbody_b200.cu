@@ -131,6 +131,7 @@ typedef void (*ForceFn)(const StepParams);
 struct KernelEntry {
     int r, kind, eqm, d2;  // kind: 0 force, 1 force + potential, 2 potential only
     ForceFn fn;
+    int mid;               // 1: the variant for worlds of few source tiles (near path unrolled deeper)
 };
 
 // <threads, R, POT, CTAs/SM, flush chunk, EQM uniform mass (no m*w multiply), D2 z == 0 (reference 2-D uploads), PONLY>
@@ -141,8 +142,11 @@ struct KernelEntry {
 // the potential accumulators of R >= 3 targets do not fit 128 registers: those variants run 3 CTAs per SM
 #define NB_KP(R, E, D) {R, 1, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false>}
 #define NB_KD(R, E, D) {R, 2, E, D, force_kernel<kNT, R, true, ((R) >= 3 ? 3 : 4) / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, true>}
+#define NB_KM(R, E, D) {R, 0, E, D, force_kernel<kNT, R, false, 4 / kCtaScale, kFlushChunk, (E) != 0, (D) != 0, false, 4>, 1}
 #define NB_ALL_ED(M, R) M(R, 0, 0), M(R, 1, 0), M(R, 0, 1), M(R, 1, 1)
 const KernelEntry kKernels[] = {
+    // ("mid" variants — R = 4 with the near path unrolled 4x deeper for worlds of few source tiles — were measured
+    //  and dropped: 1.91 vs 1.80 ms at N = 65536, profiles/r02_time_variants.txt; the selection hook stays)
     NB_ALL_ED(NB_KF, 4), NB_ALL_ED(NB_KF, 3), NB_ALL_ED(NB_KF, 2), NB_ALL_ED(NB_KF, 1),
     // with the fused potential (nb_step_with_diagnostics)
     NB_ALL_ED(NB_KP, 4), NB_ALL_ED(NB_KP, 3), NB_ALL_ED(NB_KP, 2), NB_ALL_ED(NB_KP, 1),
@@ -150,16 +154,21 @@ const KernelEntry kKernels[] = {
     NB_ALL_ED(NB_KD, 4), NB_ALL_ED(NB_KD, 2), NB_ALL_ED(NB_KD, 1),
 };
 #undef NB_KF
+#undef NB_KM
 #undef NB_KP
 #undef NB_KD
 #undef NB_ALL_ED
 constexpr int kNumKernels = sizeof(kKernels) / sizeof(kKernels[0]);
+constexpr long long kMidTiles = 256;  // worlds of <= 2^17 bodies take the "mid" variants where they exist
 
-const KernelEntry* find_kernel(int r, int kind, int eqm, int d2) {
+const KernelEntry* find_kernel(int r, int kind, int eqm, int d2, int mid = 0) {
+    const KernelEntry* plain = nullptr;
     for (int k = 0; k < kNumKernels; ++k)
-        if (kKernels[k].r == r && kKernels[k].kind == kind && kKernels[k].eqm == eqm && kKernels[k].d2 == d2)
-            return &kKernels[k];
-    return nullptr;
+        if (kKernels[k].r == r && kKernels[k].kind == kind && kKernels[k].eqm == eqm && kKernels[k].d2 == d2) {
+            if (kKernels[k].mid == mid) return &kKernels[k];
+            if (!kKernels[k].mid) plain = &kKernels[k];
+        }
+    return plain;  // no "mid" variant of this shape: the plain one
 }
 
 // Choose targets-per-thread and the source split so the grid fills whole waves of SMs.
@@ -176,7 +185,7 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
         if (honour_forced && c->forced_r != r) continue;
         // the stand-alone diagnostics count every body: its uniform-mass variant needs ALL masses equal
         const int eqm = (kind == 2 ? c->diag_uniform_mass : c->uniform_mass) ? 1 : 0, d2 = c->planar ? 1 : 0;
-        const KernelEntry* ke = find_kernel(r, kind, eqm, d2);
+        const KernelEntry* ke = find_kernel(r, kind, eqm, d2, c->n_tiles <= kMidTiles ? 1 : 0);
         if (!ke) continue;
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ke->fn, kNT, 0) != cudaSuccess || per_sm < 1)
