@@ -204,7 +204,12 @@ LaunchPlan make_plan(const nb_ctx* c, long long n_targets, long long n_src_tiles
             // larger R amortises shared-memory reads; an extra segment costs one more FP64 partial per target
             // (measured: no visible cost up to 64 segments even with 4 source tiles per CTA, N = 2^17 ... 2^20,
             // profiles/r01_time_modes.txt)
-            const double score = eff * (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90))) * (1.0 - 0.00003 * (nseg - 1));
+            // worlds of <= 128 source tiles (N <= 65536): a large share of the (warp, group) visits is "near", a warp
+            // with fewer targets per thread has a smaller clump and fewer of them, and more, shorter CTAs balance
+            // better: R = 1 measured 4-12 % faster than R = 4 there (profiles/r02_time_r_scan.txt); equal above
+            const double r_pref = c->n_tiles <= 128 ? (r == 1 ? 1.0 : (r == 2 ? 0.99 : 0.95))
+                                                    : (r == 4 ? 1.0 : (r == 3 ? 0.98 : (r == 2 ? 0.97 : 0.90)));
+            const double score = eff * r_pref * (1.0 - 0.00003 * (nseg - 1));
             if (score > best_score) {
                 best_score = score;
                 best.variant = (int)(ke - kKernels);
