@@ -209,6 +209,22 @@ int nb_step_diagnostics(nb_ctx* ctx, nb_diag* out);
  * Sharded: collective, every rank receives the global values. Synchronises. */
 int nb_compute_diagnostics(nb_ctx* ctx, nb_diag* out);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The same sums as
+ * nb_compute_diagnostics on a context in NB_PRECISION_FP64_EXACT (the FP64 kernel of that path, same operation
+ * order), without a context and without any allocation: inputs and output are DEVICE pointers the caller owns
+ * (d_pos, d_vel: n x dim doubles in the reference's component layout, dim 2 or 3; d_mass: n floats; d_out: one
+ * nb_diag), the two kernels are enqueued on `cuda_stream` (a cudaStream_t, NULL = the default stream) of device
+ * `device`, and the call returns without synchronising: read *d_out after the stream has reached that point.
+ * Scratch (per-CTA partial sums) lives in a static device array of 96 KiB that every GPU loading the library
+ * holds until exit, sized for n <= NB_NOALLOC_MAX_BODIES; a larger n returns NB_ERR_INVALID (nothing enqueued).
+ * Calls no cudaMalloc / cudaFree / allocating routine; the first call on a device looks the array's device
+ * address up (cudaGetSymbolAddress), so make one call outside a capture first. All calls on a device share the
+ * array: calls that overlap on the GPU (different streams) race on it — keep them on one stream or order them. */
+#define NB_NOALLOC_MAX_BODIES 262144
+int nb_diagnostics_noalloc(int device, int64_t n, int dim, const double* d_pos, const double* d_vel,
+                           const float* d_mass, double g, float softening, nb_diag* d_out, void* cuda_stream);
+
 /* Physics::zero_net_momentum (Physics.hpp:66-85). */
 int nb_zero_net_momentum(nb_ctx* ctx);
 

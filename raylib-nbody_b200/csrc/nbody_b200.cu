@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <set>
 #include <string>
 #include <vector>
@@ -1630,6 +1631,7 @@ extern "C" int nb_zero_net_momentum(nb_ctx* c) {
 
 #include "host_collide.cuh"  // nb_count_overlaps, nb_resolve_collisions
 #include "host_scenario.cuh"  // nb_scenario_write / nb_scenario_read
+#include "host_noalloc.cuh"   // nb_diagnostics_noalloc (static device scratch, no allocation)
 
 extern "C" int nb_reset_scenario(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_reset_scenario: null context");

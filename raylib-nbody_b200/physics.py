@@ -65,7 +65,8 @@ EXPORTS = ["nb_create", "nb_create_multi", "nb_num_devices", "nb_comm_unique_id"
            "nb_download3", "nb_download_state", "nb_stream_order", "nb_set_stream_order", "nb_num_bodies", "nb_local_range", "nb_partition", "nb_compute_gravity", "nb_integrate", "nb_step",
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt", "nb_merge_info",
            "nb_substep_plan", "nb_reset_scenario", "nb_scenario_default_config", "nb_scenario_write", "nb_scenario_read_header", "nb_scenario_read", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
-           "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned"]
+           "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned",
+           "nb_diagnostics_noalloc"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
 SOLVER_DIRECT, SOLVER_REFERENCE = 0, 1
@@ -131,6 +132,9 @@ def load_library(path=LIB_PATH):
     L.nb_step_diagnostics.argtypes = [C.c_void_p, C.POINTER(_Diag)]
     L.nb_compute_diagnostics.argtypes = [C.c_void_p, C.POINTER(_Diag)]
     L.nb_zero_net_momentum.argtypes = [C.c_void_p]
+    if hasattr(L, "nb_diagnostics_noalloc"):
+        L.nb_diagnostics_noalloc.argtypes = [C.c_int, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
+                                             C.c_float, C.c_void_p, C.c_void_p]
     L.nb_substep_plan.argtypes = [C.c_float, C.c_float, C.c_int32, _fp]
     L.nb_reset_scenario.argtypes = [C.c_void_p]
     if hasattr(L, "nb_scenario_write"):
@@ -222,6 +226,24 @@ def substep_plan(dt, max_substep, max_substeps_per_frame):
 def dt_eff(fixed_dt, time_scale):
     """dtEff = baseDt * max(0, time_scale) in float, Physics.hpp:54-55 with use_fixed_dt."""
     return float(np.float32(fixed_dt) * max(np.float32(0.0), np.float32(time_scale)))
+
+
+NOALLOC_MAX_BODIES = 262144  # NB_NOALLOC_MAX_BODIES
+DIAG_STRUCT_BYTES = C.sizeof(_Diag)
+
+
+def diagnostics_noalloc(device, n, dim, d_pos, d_vel, d_mass, g, softening, d_out, stream=0):
+    """nb_diagnostics_noalloc (no counterpart in the reference): compute_diagnostics over DEVICE arrays given as
+    integer addresses, result as one nb_diag at device address d_out; enqueues on `stream` and does not
+    synchronise, allocates nothing. diag_from_bytes() decodes the struct once it is back on the host."""
+    _check(load_library().nb_diagnostics_noalloc(device, n, dim, C.c_void_p(d_pos), C.c_void_p(d_vel), C.c_void_p(d_mass),
+                                                 C.c_double(g), C.c_float(softening), C.c_void_p(d_out),
+                                                 C.c_void_p(stream)))
+
+
+def diag_from_bytes(raw):
+    """Diagnostics from the DIAG_STRUCT_BYTES bytes of an nb_diag."""
+    return Diagnostics(_Diag.from_buffer_copy(bytes(raw)))
 
 
 def partition(n, rank, world):
