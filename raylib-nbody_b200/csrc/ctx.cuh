@@ -122,6 +122,22 @@ struct nb_ctx {
     long long bh_passes = 0, bh_nodes = 0, bh_depth = 0, bh_live = 0;
     unsigned long long bh_walk[3] = {0, 0, 0};  // cells popped, terms, exact accept tests (when bh_stats)
 
+    // ---- ownership along one Hilbert curve of the whole world (multi-GPU contexts, partition.cuh) ----
+    bool curve_partition = true;        // NB_CURVE_PARTITION=0: ranks own their upload-order rows (round 1 behaviour)
+    bool perm_valid = false;            // perm / inv_perm describe the bodies held now
+    long long uploads_since_partition = 0;
+    int* perm = nullptr;                // internal row -> upload row, all n rows, identical on every rank
+    int* inv_perm = nullptr;            // upload row -> internal row
+    double* xb = nullptr;               // exchange buffer: x, v, a, a0 of EVERY row (12 arrays of cap rows)
+    float* xb_mass = nullptr;
+    uint8_t* xb_pinned = nullptr;
+    unsigned long long* part_keys[2] = {nullptr, nullptr};
+    int* part_vals[2] = {nullptr, nullptr};
+    void* part_tmp = nullptr;
+    size_t part_tmp_bytes = 0;
+    long long part_cap = 0;             // rows the buffers above were allocated for
+    long long partitions = 0;           // times the ownership was recomputed
+
     int gen = 0;               // generation of pk[gen & 1]
     int mass_exp = 0;          // masses are packed as m * 2^-mass_exp
     bool uniform_mass = false; // every body that can attract has the same mass -> no m*w multiply in the kernel

@@ -24,6 +24,7 @@
 #include "diag.cuh"
 #include "exact.cuh"
 #include "force_kernel.cuh"
+#include "partition.cuh"
 #include "state.cuh"
 
 using namespace nb;
@@ -86,7 +87,7 @@ struct Nccl {
 Nccl g_nccl;
 
 // ncclDataType_t / ncclRedOp_t values (stable across NCCL 2.x)
-constexpr int kNcclFloat32 = 7, kNcclFloat64 = 8, kNcclUint32 = 3, kNcclSum = 0, kNcclMax = 2;
+constexpr int kNcclFloat32 = 7, kNcclFloat64 = 8, kNcclUint32 = 3, kNcclUint8 = 1, kNcclInt32 = 2, kNcclSum = 0, kNcclMax = 2;
 
 int load_nccl() {
     if (g_nccl.handle) return NB_OK;
@@ -342,6 +343,7 @@ int size_for(nb_ctx* c, long long n) {
     // upload and the packs that follow (own rows incl. padding by pack_kernel, the other ranks' by the exchange).
     const bool same_shape = !realloc_rows && c->n_sized == n;
     if (!same_shape) {
+        c->perm_valid = false;
         NB_CUDA(cudaMemsetAsync(c->state, 0, sizeof(double) * 15 * c->cap, c->stream));
         NB_CUDA(cudaMemsetAsync(c->mass, 0, sizeof(float) * c->cap, c->stream));
         // every row starts as a non-attracting row (hi_x = kFarPacked, m = 0) of a group that is never "near";
@@ -414,6 +416,7 @@ extern "C" int nb_default_config(nb_config* out) {
     return NB_OK;
 }
 
+namespace { void free_partition(nb_ctx* c); }
 static void destroy_one(nb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
@@ -421,6 +424,7 @@ static void destroy_one(nb_ctx* c) {
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     if (c->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     free_bodies(c);
+    free_partition(c);
     cudaFree(c->extent);
     cudaFree(c->l2_scratch);
     cudaFree(c->collide_scratch);
@@ -472,6 +476,7 @@ static int init_ctx(nb_ctx* c, int world) {
     if (const char* v = getenv("NB_FORCE_NSEG")) c->forced_nseg = atoi(v);
     if (const char* v = getenv("NB_RESORT_EVERY")) c->resort_every = std::max(1, atoi(v));
     if (const char* v = getenv("NB_FORCE_GENERIC")) c->force_generic = atoi(v) != 0;
+    if (const char* v = getenv("NB_CURVE_PARTITION")) c->curve_partition = atoi(v) != 0;
     return NB_OK;
 }
 
@@ -982,8 +987,194 @@ void commit_drift(nb_ctx* c) {
 }  // namespace
 
 // ---------------------------------------------------------------------------------------
+// ownership along one curve (partition.cuh): the exchange buffer and the permutation
+// ---------------------------------------------------------------------------------------
+namespace {
+
+bool uses_partition(const nb_ctx* c) { return c->world > 1 && c->curve_partition; }
+
+void free_partition(nb_ctx* c) {
+    cudaFree(c->perm); cudaFree(c->inv_perm); cudaFree(c->xb); cudaFree(c->xb_mass); cudaFree(c->xb_pinned);
+    cudaFree(c->part_tmp);
+    for (int g = 0; g < 2; ++g) { cudaFree(c->part_keys[g]); cudaFree(c->part_vals[g]); c->part_keys[g] = nullptr; c->part_vals[g] = nullptr; }
+    c->perm = c->inv_perm = nullptr; c->xb = nullptr; c->xb_mass = nullptr; c->xb_pinned = nullptr; c->part_tmp = nullptr;
+    c->part_tmp_bytes = 0; c->part_cap = 0; c->perm_valid = false;
+}
+
+// buffers for c->cap rows (called after size_for, with the device current)
+int ensure_partition_buffers(nb_ctx* c) {
+    if (!uses_partition(c) || c->part_cap >= c->cap) return NB_OK;
+    free_partition(c);
+    const size_t rows = (size_t)c->cap;
+    NB_CUDA(cudaMalloc(&c->perm, sizeof(int) * rows));
+    NB_CUDA(cudaMalloc(&c->inv_perm, sizeof(int) * rows));
+    NB_CUDA(cudaMalloc(&c->xb, sizeof(double) * kXbArrays * rows));
+    NB_CUDA(cudaMalloc(&c->xb_mass, sizeof(float) * rows));
+    NB_CUDA(cudaMalloc(&c->xb_pinned, rows));
+    for (int g = 0; g < 2; ++g) {
+        NB_CUDA(cudaMalloc(&c->part_keys[g], sizeof(unsigned long long) * rows));
+        NB_CUDA(cudaMalloc(&c->part_vals[g], sizeof(int) * rows));
+    }
+    size_t tmp = 0;
+    NB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, c->part_keys[0], c->part_keys[1], c->part_vals[0],
+                                            c->part_vals[1], (int)rows, 0, 64, c->stream));
+    NB_CUDA(cudaMalloc(&c->part_tmp, tmp ? tmp : 16));
+    c->part_tmp_bytes = tmp;
+    c->part_cap = c->cap;
+    return NB_OK;
+}
+
+// every device's exchange buffer as seen from member s: its own first, then the peers' (one process, several GPUs)
+XbOut xb_out(nb_ctx* s) {
+    XbOut o;
+    memset(&o, 0, sizeof(o));
+    auto add = [&](nb_ctx* t) { o.st[o.n] = t->xb; o.mass[o.n] = t->xb_mass; o.pinned[o.n] = t->xb_pinned; o.n++; };
+    add(s);
+    if (s->group)
+        for (nb_ctx* t : s->group->m)
+            if (t != s) add(t);
+    return o;
+}
+
+// NCCL contexts: all-gather (in place) the slices [rank * rows, (rank + 1) * rows) of XB arrays [a0, a1) and,
+// when asked, of the mass / pinned rows. `src` != nullptr: array a's slice comes from src[a] instead (row 0 of
+// the slice). Collective: every rank calls it, rows or not.
+int allgather_xb(nb_ctx* c, int a0, int a1, bool with_mass, double* const* src = nullptr) {
+    const size_t rows = (size_t)c->tiles_per_rank * kTileBodies;
+    NB_NCCL(g_nccl.GroupStart());
+    for (int a = a0; a < a1; ++a) {
+        double* arr = c->xb + (size_t)a * c->cap;
+        const double* send = src ? src[a] : arr + (size_t)c->rank * rows;
+        NB_NCCL(g_nccl.AllGather(send, arr, rows, kNcclFloat64, c->nccl_comm, c->stream));
+    }
+    if (with_mass) {
+        NB_NCCL(g_nccl.AllGather(c->xb_mass + (size_t)c->rank * rows, c->xb_mass, rows, kNcclFloat32, c->nccl_comm, c->stream));
+        NB_NCCL(g_nccl.AllGather(c->xb_pinned + (size_t)c->rank * rows, c->xb_pinned, rows, kNcclUint8, c->nccl_comm, c->stream));
+    }
+    NB_NCCL(g_nccl.GroupEnd());
+    return NB_OK;
+}
+
+// Every rank's XB <- the rows each rank owns (internal order): state arrays [0, n_arrays) and, when asked, masses
+// and pinned flags.
+int publish_owned(nb_ctx* c, int n_arrays, bool with_mass) {
+    const Team team(c);
+    if (c->group) {
+        NB_TRY(team_barrier(c));  // nobody still reads the previous contents
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            const long long n_local = s->hi - s->lo;
+            if (n_local <= 0) continue;
+            publish_state_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                s->view(), n_arrays, with_mass, s->cap, xb_out(s));
+            NB_CUDA(cudaGetLastError());
+            s->kernel_launches++;
+        }
+        return team_barrier(c);
+    }
+    const size_t row0 = (size_t)c->rank * c->tiles_per_rank * kTileBodies;
+    double* src[kXbArrays];
+    for (int k = 0; k < 3; ++k) {
+        src[k] = c->pos_slot(c->x_sel, k) + row0;
+        src[3 + k] = c->sx(3 + k) + row0;
+        src[6 + k] = c->sx(6 + k) + row0;
+        src[9 + k] = c->sx(9 + k) + row0;
+    }
+    if (with_mass) {  // in-place slices of the mass / pinned gathers
+        const size_t rows = (size_t)c->tiles_per_rank * kTileBodies;
+        NB_CUDA(cudaMemcpyAsync(c->xb_mass + row0, c->mass + row0, sizeof(float) * rows, cudaMemcpyDeviceToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(c->xb_pinned + row0, c->pinned + row0, rows, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return allgather_xb(c, 0, n_arrays, with_mass, src);
+}
+
+// perm <- all n bodies along one Hilbert curve of the positions in XB (arrays 0-5: x, v; xb_mass). XB rows are
+// upload rows (through == nullptr) or the previous internal rows (through == the previous perm, copied).
+// Every rank computes the same permutation from the same data: no communication.
+int compute_perm(nb_ctx* s, const int* through) {
+    const long long n = s->n;
+    NB_CUDA(cudaMemsetAsync(s->extent + kPartitionExtentSlot, 0, sizeof(unsigned int), s->stream));
+    const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n, kStateThreads), 4 * s->sm_count);
+    xb_extent_kernel<<<grid, kStateThreads, 0, s->stream>>>(s->xb, s->cap, n, s->xb_mass, s->extent);
+    if (s->dim == 2)
+        xb_curve_key_kernel<2><<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(
+            s->xb, s->cap, n, s->xb_mass, s->extent, s->part_keys[0], s->part_vals[0]);
+    else
+        xb_curve_key_kernel<3><<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(
+            s->xb, s->cap, n, s->xb_mass, s->extent, s->part_keys[0], s->part_vals[0]);
+    size_t tmp = s->part_tmp_bytes;
+    NB_CUDA(cub::DeviceRadixSort::SortPairs(s->part_tmp, tmp, s->part_keys[0], s->part_keys[1], s->part_vals[0],
+                                            s->part_vals[1], (int)n, 0, 64, s->stream));
+    set_perm_kernel<<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(s->part_vals[1], through, n, s->perm,
+                                                                                   s->inv_perm);
+    NB_CUDA(cudaGetLastError());
+    s->kernel_launches += 4;
+    s->perm_valid = true;
+    s->uploads_since_partition = 0;
+    s->partitions++;
+    return NB_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------
 // state upload / download
 // ---------------------------------------------------------------------------------------
+// Multi-GPU contexts that own stretches of one curve (partition.cuh): every rank copies ITS upload rows [lo,hi)
+// from the host as before, the ranks exchange them over NVLink, and each keeps the bodies of its stretch.
+static int upload_partitioned(nb_ctx* c, const double* pos, const double* vel, const float* mass,
+                              const uint8_t* pinned, int dim, const double* acc) {
+    const Team team(c);
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_TRY(ensure_partition_buffers(s));
+    }
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long rows = s->hi - s->lo;
+        if (rows <= 0) continue;
+        const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)rows;
+        const size_t off = (size_t)s->lo * dim;
+        NB_TRY(ensure_staging(s, 3 * vec_bytes));
+        double* d_pos = static_cast<double*>(s->staging);
+        double* d_vel = d_pos + (size_t)dim * rows;
+        double* d_acc = d_vel + (size_t)dim * rows;
+        NB_CUDA(cudaMemcpyAsync(d_pos, pos + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+        NB_CUDA(cudaMemcpyAsync(d_vel, vel + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+        if (acc) NB_CUDA(cudaMemcpyAsync(d_acc, acc + off, vec_bytes, cudaMemcpyHostToDevice, s->stream));
+        NB_CUDA(cudaMemcpyAsync(s->xb_mass + s->lo, mass + s->lo, sizeof(float) * rows, cudaMemcpyHostToDevice, s->stream));
+        if (pinned)
+            NB_CUDA(cudaMemcpyAsync(s->xb_pinned + s->lo, pinned + s->lo, (size_t)rows, cudaMemcpyHostToDevice, s->stream));
+        else
+            NB_CUDA(cudaMemsetAsync(s->xb_pinned + s->lo, 0, (size_t)rows, s->stream));
+        unpack_aos_xb_kernel<<<blocks_for(rows, kStateThreads), kStateThreads, 0, s->stream>>>(
+            d_pos, d_vel, acc ? d_acc : nullptr, dim, s->lo, rows, s->cap, xb_out(s));
+        NB_CUDA(cudaGetLastError());
+        s->kernel_launches++;
+    }
+    if (c->group) NB_TRY(team_barrier(c));
+    else NB_TRY(allgather_xb(c, 0, 9, true));
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        // a re-upload of a world of the same size keeps the ownership (the caller's per-frame pattern: the bodies
+        // have moved a step, the curve order is as good as before); it is recomputed every 64th time
+        if (!s->perm_valid || ++s->uploads_since_partition >= 64) NB_TRY(compute_perm(s, nullptr));
+        const long long n_local = s->hi - s->lo;
+        if (n_local > 0) {
+            gather_owned_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                s->xb, s->xb_mass, s->xb_pinned, s->cap, s->perm, nullptr, 9, s->view(), s->mass, s->pinned);
+            NB_CUDA(cudaGetLastError());
+            s->kernel_launches++;
+        }
+        s->acc_valid = acc != nullptr;
+    }
+    for (nb_ctx* s : team) {  // the borrowed host arrays may be pageable
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+    }
+    return NB_OK;
+}
+
 static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel, const float* mass,
                       const uint8_t* pinned, int dim, const double* acc = nullptr) {
     if (!c) return fail(NB_ERR_INVALID, "nb_upload: null context");
@@ -1024,6 +1215,7 @@ static int upload_dim(nb_ctx* c, int64_t n, const double* pos, const double* vel
         s->step_diag_valid = false;
     }
     if (n == 0) return NB_OK;
+    if (uses_partition(c)) return upload_partitioned(c, pos, vel, mass, pinned, dim, acc);
     // a rank only needs the FP64 state of its own targets: the other bodies reach it as FP32 sources
     // through the exchange of the packed stream (prepare_packed), so only rows [lo,hi) are copied
     for (nb_ctx* s : team) {
@@ -1077,6 +1269,35 @@ static int download_dim(nb_ctx* c, double* pos, double* vel, double* acc, int di
     if (!c) return fail(NB_ERR_INVALID, "nb_download: null context");
     const Team team(c);
     double* out[4] = {pos, vel, acc, acc_prev};
+    if (uses_partition(c) && c->n > 0 && c->perm_valid) {
+        // the rows a rank downloads are upload rows [lo,hi); their bodies live wherever the curve put them:
+        // publish every rank's owned rows, then read the wanted ones through inv_perm
+        int n_arrays = 0;
+        for (int w = 0; w < 4; ++w)
+            if (out[w]) n_arrays = 3 * (w + 1);
+        if (n_arrays > 0) NB_TRY(publish_owned(c, n_arrays, false));
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            const long long n_local = s->hi - s->lo;
+            if (n_local <= 0) continue;
+            const size_t vec_bytes = sizeof(double) * (size_t)dim * (size_t)n_local;
+            NB_TRY(ensure_staging(s, 4 * vec_bytes));
+            for (int w = 0; w < 4; ++w) {
+                if (!out[w]) continue;
+                double* d = static_cast<double*>(s->staging) + (size_t)w * dim * n_local;
+                pack_aos_xb_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                    s->xb, s->cap, s->inv_perm, w, dim, s->lo, s->hi, d);
+                s->kernel_launches++;
+                NB_CUDA(cudaMemcpyAsync(out[w] + (size_t)s->lo * dim, d, vec_bytes, cudaMemcpyDeviceToHost, s->stream));
+            }
+        }
+        for (nb_ctx* s : team) {
+            NB_CUDA(cudaSetDevice(s->device));
+            NB_CUDA(cudaStreamSynchronize(s->stream));
+            s->absorb_filter_flip();
+        }
+        return NB_OK;
+    }
     for (nb_ctx* s : team) {  // every member fills its own rows of the caller's arrays
         NB_CUDA(cudaSetDevice(s->device));
         const long long n_local = s->hi - s->lo;
@@ -1115,6 +1336,20 @@ extern "C" int nb_download_state(nb_ctx* c, int dim, double* pos, double* vel, d
 // bit-identical to the uninterrupted one carries it (scenarios.save_snapshot / load_snapshot).
 extern "C" int nb_stream_order(nb_ctx* c, int32_t* order, int64_t* generations_since_sort) {
     if (!c || !order) return fail(NB_ERR_INVALID, "nb_stream_order: null");
+    if (uses_partition(c) && c->perm_valid) {  // stream row -> internal row -> the caller's (upload) row
+        for (nb_ctx* s : Team(c)) {
+            NB_CUDA(cudaSetDevice(s->device));
+            const long long n_local = s->hi - s->lo;
+            if (n_local > 0) {
+                map_rows_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                    s->order, s->perm, s->lo, s->hi, s->part_vals[0]);
+                NB_CUDA(cudaMemcpyAsync(order + s->lo, s->part_vals[0] + s->lo, sizeof(int) * n_local, cudaMemcpyDeviceToHost, s->stream));
+            }
+            NB_CUDA(cudaStreamSynchronize(s->stream));
+        }
+        if (generations_since_sort) *generations_since_sort = c->packs_since_sort;
+        return NB_OK;
+    }
     for (nb_ctx* s : Team(c)) {
         NB_CUDA(cudaSetDevice(s->device));
         const long long n_local = s->hi - s->lo;
@@ -1126,9 +1361,61 @@ extern "C" int nb_stream_order(nb_ctx* c, int32_t* order, int64_t* generations_s
     return NB_OK;
 }
 
+// Multi-GPU contexts with ownership along the curve: the stream order IS the ownership (stream row k of the
+// whole world belongs to the rank whose range holds k), so restoring it moves bodies between ranks: publish the
+// state every rank holds, make the given order the new permutation, fetch the rows this rank now owns.
+static int set_stream_order_partitioned(nb_ctx* c, const int32_t* order, int64_t generations_since_sort) {
+    const Team team(c);
+    const long long n = c->n;
+    for (nb_ctx* s : team) {  // entries a context reads: its own range (one process per GPU) or all (one process)
+        const long long q0 = s->lo, q1 = s->hi;
+        for (long long q = q0; q < q1; ++q)
+            if (order[q] < 0 || order[q] >= n) return fail(NB_ERR_INVALID, "nb_set_stream_order: row out of range");
+    }
+    if (c->group) {
+        std::vector<uint8_t> seen((size_t)n, 0);
+        for (long long q = 0; q < n; ++q) {
+            if (seen[(size_t)order[q]]) return fail(NB_ERR_INVALID, "nb_set_stream_order: not a permutation");
+            seen[(size_t)order[q]] = 1;
+        }
+    }
+    NB_TRY(publish_owned(c, kXbArrays, true));  // XB: every body's state, previous internal order
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        const long long n_local = s->hi - s->lo;
+        int* fresh = s->part_vals[0];
+        if (c->group) {
+            NB_CUDA(cudaMemcpyAsync(fresh, order, sizeof(int) * n, cudaMemcpyHostToDevice, s->stream));
+        } else {
+            const size_t rows = (size_t)s->tiles_per_rank * kTileBodies;
+            if (n_local > 0)
+                NB_CUDA(cudaMemcpyAsync(fresh + s->lo, order + s->lo, sizeof(int) * n_local, cudaMemcpyHostToDevice, s->stream));
+            NB_NCCL(g_nccl.AllGather(fresh + (size_t)s->rank * rows, fresh, rows, kNcclInt32, s->nccl_comm, s->stream));
+        }
+        if (n_local > 0) {
+            gather_owned_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                s->xb, s->xb_mass, s->xb_pinned, s->cap, fresh, s->inv_perm, kXbArrays, s->view(), s->mass, s->pinned);
+            iota_order_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(s->order, s->lo, s->hi);
+        }
+        set_perm_kernel<<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(fresh, nullptr, n, s->perm, s->inv_perm);
+        NB_CUDA(cudaGetLastError());
+        s->kernel_launches += 3;
+    }
+    for (nb_ctx* s : team) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_CUDA(cudaStreamSynchronize(s->stream));
+        s->order_valid = true;
+        s->packs_since_sort = generations_since_sort;
+        s->packed_valid = false; s->drop_speculation();
+        s->step_diag_valid = false;
+    }
+    return NB_OK;
+}
+
 extern "C" int nb_set_stream_order(nb_ctx* c, const int32_t* order, int64_t generations_since_sort) {
     if (!c || !order) return fail(NB_ERR_INVALID, "nb_set_stream_order: null");
     if (generations_since_sort < 0) return fail(NB_ERR_INVALID, "nb_set_stream_order: negative age");
+    if (uses_partition(c) && c->perm_valid) return set_stream_order_partitioned(c, order, generations_since_sort);
     for (nb_ctx* s : Team(c)) {
         const long long n_local = s->hi - s->lo;
         // the rows a context owns must be a permutation of themselves

@@ -131,3 +131,127 @@ def test_single_process_multi_gpu_matches_single_gpu(pkg, n_dev, n, integ):
     assert np.abs(s1[1] - s2[1]).max() / np.abs(s1[1]).max() <= 1e-9
     assert np.abs(s1[2] - s2[2]).max() / np.abs(s1[2]).max() <= 1e-6
     assert np.abs(f1 - f2)[:3].max() <= 1e-7 * abs(f1[2]) and np.abs(a1 - a2)[:3].max() <= 1e-7 * abs(a1[2])
+
+
+# ---- ownership along one curve (csrc/partition.cuh): the interface still speaks upload rows -----------------
+@pytest.mark.parametrize("n_dev,n,dim", [(2, 5000, 3), (2, 700, 2), (3, 1500, 3), (8, 9000, 3), (2, 3, 2)])
+def test_multi_gpu_upload_download_round_trip_is_exact(pkg, n_dev, n, dim):
+    """Every GPU owns a stretch of one Hilbert curve of the whole world, so uploaded rows move between GPUs
+    (csrc/partition.cuh). What the caller sees must not change: a download returns the uploaded rows, bit for bit,
+    in the caller's order — also after a re-upload of a same-sized world, which re-uses the ownership."""
+    if _n_gpus() < n_dev:
+        pytest.skip(f"needs {n_dev} GPUs")
+    rng = np.random.default_rng(n)
+    ph = pkg.Physics(devices=list(range(n_dev)))
+    ph.set_precision(pkg.PRECISION_FP32)
+    for trial in range(3):
+        pos = rng.standard_normal((n, dim)) * 1e8
+        vel = rng.standard_normal((n, dim)) * 1e3
+        acc = rng.standard_normal((n, dim))
+        mass = rng.uniform(1e20, 1e24, n).astype(np.float32)
+        pinned = (rng.uniform(size=n) < 0.1).astype(np.uint8)
+        ph.upload_state(pos, vel, acc, mass, pinned)
+        p, v, a, a0 = ph.download_state()
+        assert np.array_equal(p, pos) and np.array_equal(v, vel) and np.array_equal(a, acc) and not a0.any()
+    # pinned flags and masses followed their bodies: one Euler frame moves exactly the bodies that are not pinned
+    ph.set_config(integrator=0, softening=1e7)
+    ph.upload(pos, vel, mass, pinned)
+    ph.step(1.0, 1)
+    p1 = ph.download()[0]
+    moved = np.any(p1 != pos, axis=1)
+    assert np.array_equal(moved, pinned == 0)
+    ph.close()
+
+
+@pytest.mark.parametrize("integ", [1, 0])
+def test_multi_gpu_checkpoint_resume_is_bit_exact(pkg, integ):
+    """The stream order of a multi-GPU context names the caller's rows and fixes which GPU owns which body:
+    state + stream order resume a run bit for bit in a fresh context (test_checkpoint_resume_is_bit_exact on 2 GPUs)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    n = 6000
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=31, dim=3)
+    eps = 3.844e8 / np.sqrt(n)
+    dt = 1e-3 * pkg.scenarios.crossing_time(n)
+
+    def fresh():
+        ph = pkg.Physics(devices=[0, 1])
+        ph.set_precision(pkg.PRECISION_FP32)
+        ph.set_config(softening=eps, integrator=integ)
+        return ph
+
+    a = fresh()
+    a.upload(pos, vel, mass)
+    a.step(dt, 6)
+    full = a.download_state()
+    a.close()
+    b = fresh()
+    b.upload(pos, vel, mass)
+    b.step(dt, 3)
+    p, v, acc, acc_prev = b.download_state()
+    order, age = b.stream_order()
+    b.close()
+    assert np.array_equal(np.sort(order), np.arange(n))  # a permutation of the caller's rows
+    c = fresh()
+    c.upload_state(p, v, acc if integ == 1 else None, mass)
+    c.set_stream_order(order, age)
+    c.step(dt, 3)
+    resumed = c.download_state()
+    c.close()
+    for k in range(3):
+        assert np.array_equal(resumed[k], full[k]), k
+
+
+def _worker_round_trip(rank, world, n, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    pkg = ge.load_package()
+    torch.cuda.set_device(rank)
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank),
+                            init_method="file://" + os.path.join(out_dir, "rendezvous"))
+    try:
+        pos, vel, mass = pkg.scenarios.plummer(n, seed=5, dim=3)
+        eps = 3.844e8 / np.sqrt(n)
+        dt = 1e-3 * pkg.scenarios.crossing_time(n)
+        ph = pkg.sharded.create(dist, rank)
+        ph.set_precision(pkg.PRECISION_FP32)
+        ph.set_config(softening=eps)
+        acc0 = np.random.default_rng(1).standard_normal(pos.shape)
+        ph.upload_state(pos, vel, acc0, mass)
+        back = [pkg.sharded.gather_rows(dist, a, n) for a in ph.download_state()[:3]]
+        exact = all(np.array_equal(x, y) for x, y in zip(back, (pos, vel, acc0)))
+        # uninterrupted run / checkpoint after 3 frames / resume in a fresh context
+        ph.upload(pos, vel, mass)
+        ph.step(dt, 3)
+        mid = [pkg.sharded.gather_rows(dist, a, n) for a in ph.download_state()]
+        order, age = ph.stream_order()          # this rank's rows [lo,hi) only
+        ph.step(dt, 3)
+        full = [pkg.sharded.gather_rows(dist, a, n) for a in ph.download_state()]
+        ph.close()
+        ph = pkg.sharded.create(dist, rank)
+        ph.set_precision(pkg.PRECISION_FP32)
+        ph.set_config(softening=eps)
+        ph.upload_state(mid[0], mid[1], mid[2], mass)
+        ph.set_stream_order(order, age)
+        ph.step(dt, 3)
+        resumed = [pkg.sharded.gather_rows(dist, a, n) for a in ph.download_state()]
+        ph.close()
+        same = all(np.array_equal(x, y) for x, y in zip(resumed[:3], full[:3]))
+        if rank == 0:
+            np.savez(os.path.join(out_dir, "round_trip.npz"), exact=exact, same=same)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 6000), (3, 1700)])
+def test_sharded_round_trip_and_resume(pkg, tmp_path, world, n):
+    """One process per GPU: downloads return the uploaded rows exactly although the bodies live on other ranks,
+    and state + per-rank stream order resume a run bit for bit."""
+    if _n_gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    mp.spawn(_worker_round_trip, args=(world, n, str(tmp_path)), nprocs=world, join=True)
+    got = np.load(tmp_path / "round_trip.npz")
+    assert bool(got["exact"]) and bool(got["same"])
