@@ -174,6 +174,14 @@ int nb_download_state(nb_ctx* ctx, int dim, double* pos, double* vel, double* ac
 int nb_stream_order(nb_ctx* ctx, int32_t* order, int64_t* generations_since_sort);
 int nb_set_stream_order(nb_ctx* ctx, const int32_t* order, int64_t generations_since_sort);
 
+/* Who owns which body in a multi-GPU context (nb_create_multi, nb_create_sharded) is the library's business: the
+ * interface keeps speaking the caller's rows (uploads and downloads of rows [lo,hi), nb_local_range), while
+ * every GPU computes the targets of one stretch of a Hilbert curve through the whole world (compact groups, few
+ * two-float visits) and the rows travel between GPUs over NVLink at upload, download, and whenever the stream is
+ * re-sorted. values[4] = {ownership along the curve in use (0 for one GPU or NB_CURVE_PARTITION=0), times the
+ * ownership was computed, same-size uploads that re-used it since, Hilbert sorts of the stream}. */
+int nb_partition_info(nb_ctx* ctx, int64_t* values);
+
 int64_t nb_num_bodies(nb_ctx* ctx);
 int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);
 /* The target partition a sharded context uses: contiguous, aligned to the 512-body source

@@ -769,9 +769,17 @@ int sort_stream(nb_ctx* c, int slot) {
     return NB_OK;
 }
 
+bool uses_partition(const nb_ctx* c);
+int repartition(nb_ctx* c);
+
 // Measure the extent of the current positions, open a new generation and pack it (the whole team).
 int prepare_packed(nb_ctx* c) {
     const Team team(c);
+    // multi-GPU contexts: when the stream is due for a re-sort, the ranks also regroup along the curve of the
+    // current positions (partition.cuh); every rank takes this decision from the same counters
+    if (uses_partition(c) && c->perm_valid && c->order_valid && c->packs_since_sort >= c->resort_every &&
+        c->n > kGroupBodies)
+        NB_TRY(repartition(c));
     for (nb_ctx* s : team) {
         NB_CUDA(cudaSetDevice(s->device));
         s->gen += 1;
@@ -1041,6 +1049,8 @@ XbOut xb_out(nb_ctx* s) {
 // the slice). Collective: every rank calls it, rows or not.
 int allgather_xb(nb_ctx* c, int a0, int a1, bool with_mass, double* const* src = nullptr) {
     const size_t rows = (size_t)c->tiles_per_rank * kTileBodies;
+    // an exchange of the packed stream may still be running on the communication stream: one collective at a time
+    NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     NB_NCCL(g_nccl.GroupStart());
     for (int a = a0; a < a1; ++a) {
         double* arr = c->xb + (size_t)a * c->cap;
@@ -1088,30 +1098,59 @@ int publish_owned(nb_ctx* c, int n_arrays, bool with_mass) {
     return allgather_xb(c, 0, n_arrays, with_mass, src);
 }
 
-// perm <- all n bodies along one Hilbert curve of the positions in XB (arrays 0-5: x, v; xb_mass). XB rows are
-// upload rows (through == nullptr) or the previous internal rows (through == the previous perm, copied).
-// Every rank computes the same permutation from the same data: no communication.
-int compute_perm(nb_ctx* s, const int* through) {
+// perm <- all n bodies along one Hilbert curve of the positions in XB (arrays 0-5: x, v; xb_mass).
+// regroup == false: XB rows are upload rows (an upload). regroup == true: XB rows are the internal rows held until
+// now (publish_owned): the rows this rank owns from now on are fetched from XB as well, with everything that
+// belongs to a body. Every rank computes the same permutation from the same data: no communication.
+int compute_perm(nb_ctx* s, bool regroup) {
     const long long n = s->n;
     NB_CUDA(cudaMemsetAsync(s->extent + kPartitionExtentSlot, 0, sizeof(unsigned int), s->stream));
     const unsigned int grid = (unsigned int)std::min<long long>(blocks_for(n, kStateThreads), 4 * s->sm_count);
     xb_extent_kernel<<<grid, kStateThreads, 0, s->stream>>>(s->xb, s->cap, n, s->xb_mass, s->extent);
+    const int* row_of = regroup ? s->inv_perm : nullptr;
     if (s->dim == 2)
         xb_curve_key_kernel<2><<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(
-            s->xb, s->cap, n, s->xb_mass, s->extent, s->part_keys[0], s->part_vals[0]);
+            s->xb, s->cap, n, s->xb_mass, row_of, s->extent, s->part_keys[0], s->part_vals[0]);
     else
         xb_curve_key_kernel<3><<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(
-            s->xb, s->cap, n, s->xb_mass, s->extent, s->part_keys[0], s->part_vals[0]);
+            s->xb, s->cap, n, s->xb_mass, row_of, s->extent, s->part_keys[0], s->part_vals[0]);
     size_t tmp = s->part_tmp_bytes;
     NB_CUDA(cub::DeviceRadixSort::SortPairs(s->part_tmp, tmp, s->part_keys[0], s->part_keys[1], s->part_vals[0],
                                             s->part_vals[1], (int)n, 0, 64, s->stream));
-    set_perm_kernel<<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(s->part_vals[1], through, n, s->perm,
-                                                                                   s->inv_perm);
+    const int* sorted = s->part_vals[1];  // XB row of the body at each place of the curve
+    const int* through = nullptr;
+    if (regroup) {
+        const long long n_local = s->hi - s->lo;
+        if (n_local > 0) {
+            gather_owned_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
+                s->xb, s->xb_mass, s->xb_pinned, s->cap, sorted, nullptr, kXbArrays, s->view(), s->mass, s->pinned);
+            s->kernel_launches++;
+        }
+        // XB row -> upload row is the permutation held until now; set_perm_kernel overwrites it in place
+        int* held = reinterpret_cast<int*>(s->part_keys[0]);  // the unsorted keys are no longer needed
+        NB_CUDA(cudaMemcpyAsync(held, s->perm, sizeof(int) * n, cudaMemcpyDeviceToDevice, s->stream));
+        through = held;
+    }
+    set_perm_kernel<<<blocks_for(n, kStateThreads), kStateThreads, 0, s->stream>>>(sorted, through, n, s->perm, s->inv_perm);
     NB_CUDA(cudaGetLastError());
     s->kernel_launches += 4;
     s->perm_valid = true;
     s->uploads_since_partition = 0;
     s->partitions++;
+    return NB_OK;
+}
+
+// Long runs: bodies leave the stretch of the curve their rank was given at upload. At every re-sort of the stream
+// the ranks publish what they hold, recompute the curve from the current positions and regroup.
+int repartition(nb_ctx* c) {
+    NB_TRY(publish_owned(c, kXbArrays, true));
+    for (nb_ctx* s : Team(c)) {
+        NB_CUDA(cudaSetDevice(s->device));
+        NB_TRY(compute_perm(s, true));
+        s->order_valid = false;  // the rows changed hands: the stream order is rebuilt by the sort that follows
+        iota_order_kernel<<<blocks_for(s->cap, kStateThreads), kStateThreads, 0, s->stream>>>(s->order, 0, s->cap);
+        NB_CUDA(cudaGetLastError());
+    }
     return NB_OK;
 }
 
@@ -1158,7 +1197,7 @@ static int upload_partitioned(nb_ctx* c, const double* pos, const double* vel, c
         NB_CUDA(cudaSetDevice(s->device));
         // a re-upload of a world of the same size keeps the ownership (the caller's per-frame pattern: the bodies
         // have moved a step, the curve order is as good as before); it is recomputed every 64th time
-        if (!s->perm_valid || ++s->uploads_since_partition >= 64) NB_TRY(compute_perm(s, nullptr));
+        if (!s->perm_valid || ++s->uploads_since_partition >= 64) NB_TRY(compute_perm(s, false));
         const long long n_local = s->hi - s->lo;
         if (n_local > 0) {
             gather_owned_kernel<<<blocks_for(n_local, kStateThreads), kStateThreads, 0, s->stream>>>(
@@ -1412,6 +1451,15 @@ static int set_stream_order_partitioned(nb_ctx* c, const int32_t* order, int64_t
     return NB_OK;
 }
 
+extern "C" int nb_partition_info(nb_ctx* c, int64_t* values) {
+    if (!c || !values) return fail(NB_ERR_INVALID, "nb_partition_info: null");
+    values[0] = uses_partition(c) ? 1 : 0;
+    values[1] = c->partitions;
+    values[2] = c->uploads_since_partition;
+    values[3] = c->sorts;
+    return NB_OK;
+}
+
 extern "C" int nb_set_stream_order(nb_ctx* c, const int32_t* order, int64_t generations_since_sort) {
     if (!c || !order) return fail(NB_ERR_INVALID, "nb_set_stream_order: null");
     if (generations_since_sort < 0) return fail(NB_ERR_INVALID, "nb_set_stream_order: negative age");
@@ -1579,6 +1627,9 @@ static int verlet_substeps(nb_ctx* c, double h, long long n_sub, bool pot) {
                     s->kernel_launches++;
                 }
                 s->packed_valid = false; s->drop_speculation();
+                // a generation like the ones commit_drift() counts: the stream is re-sorted at the same frame
+                // whether this drift was prepared by the last kick or not (a resumed run equals the uninterrupted one)
+                if (s->order_valid) s->packs_since_sort++;
             }
         }
         NB_TRY(force_pass(c, kVerletKickDrift, pot && (k + 1 == n_sub), h));

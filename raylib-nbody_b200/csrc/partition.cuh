@@ -86,14 +86,19 @@ __global__ void __launch_bounds__(kStateThreads) xb_extent_kernel(const double* 
     }
 }
 
-// Hilbert key of every row of XB (rows are in `row_of` terms: vals[i] = i), ~0 for rows the gather filter drops:
-// they sort to the end of the curve and land on the last rank(s).
+// Hilbert key of every body, ~0 for bodies the gather filter drops: they sort to the end of the curve and land on
+// the last rank(s). Pair j is the body of UPLOAD row j, whatever order XB is in (row_of == nullptr: XB is in upload
+// order; else XB row row_of[j]), and vals[j] = its XB row: the stable sort then breaks ties between bodies of one
+// curve cell by upload row, so the permutation depends on the positions only, not on who held the rows before
+// (a resumed run re-partitions exactly like the uninterrupted one).
 template <int DIMS>
 __global__ void __launch_bounds__(kStateThreads) xb_curve_key_kernel(const double* xb, long long cap, long long n,
-                                                                     const float* mass, const unsigned int* extent,
+                                                                     const float* mass, const int* row_of,
+                                                                     const unsigned int* extent,
                                                                      unsigned long long* keys, int* vals) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const long long i = row_of ? row_of[j] : j;
     const double x[3] = {xb[i], xb[cap + i], xb[2 * cap + i]};
     const double v[3] = {xb[3 * cap + i], xb[4 * cap + i], xb[5 * cap + i]};
     unsigned long long key = ~0ull;
@@ -107,8 +112,8 @@ __global__ void __launch_bounds__(kStateThreads) xb_curve_key_kernel(const doubl
             c[k] = (unsigned int)fmin(fmax(__dmul_rn(x[k], inv) + half, 0.0), 2.0 * half - 1.0);
         key = hilbert_key<DIMS>(c, kBits);
     }
-    keys[i] = key;
-    vals[i] = (int)i;
+    keys[j] = key;
+    vals[j] = (int)i;
 }
 
 // perm[k] = through ? through[sorted[k]] : sorted[k];  inv[perm[k]] = k

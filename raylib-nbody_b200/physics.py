@@ -66,7 +66,7 @@ EXPORTS = ["nb_create", "nb_create_multi", "nb_num_devices", "nb_comm_unique_id"
            "nb_step_with_diagnostics", "nb_step_diagnostics", "nb_compute_diagnostics", "nb_zero_net_momentum", "nb_count_overlaps", "nb_resolve_collisions", "nb_debug_cbrt", "nb_merge_info",
            "nb_substep_plan", "nb_reset_scenario", "nb_scenario_default_config", "nb_scenario_write", "nb_scenario_read_header", "nb_scenario_read", "nb_synchronize", "nb_timer_begin", "nb_timer_end", "nb_counters",
            "nb_profile_forces", "nb_profile_read", "nb_near_stats", "nb_overlap_profile", "nb_device_info", "nb_flush_l2", "nb_alloc_pinned", "nb_free_pinned",
-           "nb_diagnostics_noalloc"]
+           "nb_diagnostics_noalloc", "nb_partition_info"]
 
 PRECISION_AUTO, PRECISION_FP32, PRECISION_FP64_EXACT = 0, 1, 2
 SOLVER_DIRECT, SOLVER_REFERENCE = 0, 1
@@ -468,6 +468,13 @@ class Physics:
         age = C.c_int64()
         _check(self._L.nb_stream_order(self._h, order.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(age)))
         return order, age.value
+
+    def partition_info(self):
+        """nb_partition_info: dict(curve, partitions, uploads_since, sorts) of a (multi-GPU) context."""
+        v = (C.c_int64 * 4)()
+        self._L.nb_partition_info.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        _check(self._L.nb_partition_info(self._h, v))
+        return {"curve": bool(v[0]), "partitions": int(v[1]), "uploads_since": int(v[2]), "sorts": int(v[3])}
 
     def set_stream_order(self, order, generations_since_sort=0):
         order = np.ascontiguousarray(order, np.int32)

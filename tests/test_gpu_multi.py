@@ -246,12 +246,71 @@ def _worker_round_trip(rank, world, n, out_dir):
 
 
 @pytest.mark.parametrize("world,n", [(2, 6000), (3, 1700)])
-def test_sharded_round_trip_and_resume(pkg, tmp_path, world, n):
+def test_sharded_round_trip_and_resume(pkg, tmp_path, monkeypatch, world, n):
     """One process per GPU: downloads return the uploaded rows exactly although the bodies live on other ranks,
     and state + per-rank stream order resume a run bit for bit."""
     if _n_gpus() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
+    monkeypatch.setenv("NB_RESORT_EVERY", "4")   # the ranks regroup along the curve inside the 6-frame run
     mp.spawn(_worker_round_trip, args=(world, n, str(tmp_path)), nprocs=world, join=True)
     got = np.load(tmp_path / "round_trip.npz")
     assert bool(got["exact"]) and bool(got["same"])
+
+
+@pytest.mark.parametrize("integ", [1, 0])
+def test_multi_gpu_regroups_along_the_curve_during_a_run(pkg, monkeypatch, integ):
+    """Long runs: at every re-sort of the stream (here every 3 generations instead of 64) the GPUs publish what
+    they hold, recompute the curve from the current positions and regroup. The run still tracks the single-GPU
+    run, downloads still return the caller's rows, and a checkpoint taken between two regroupings resumes bit for
+    bit (ties inside one curve cell are broken by the caller's row, not by who held the body)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    monkeypatch.setenv("NB_RESORT_EVERY", "3")
+    n = 7000
+    pos, vel, mass = pkg.scenarios.plummer(n, seed=23, dim=3)
+    pinned = np.zeros(n, np.uint8)
+    pinned[::97] = 1
+    eps = 3.844e8 / np.sqrt(n)
+    dt = 2e-3 * pkg.scenarios.crossing_time(n)
+
+    def fresh(devices):
+        ph = pkg.Physics(0) if devices is None else pkg.Physics(devices=devices)
+        ph.set_precision(pkg.PRECISION_FP32)
+        ph.set_config(softening=eps, integrator=integ)
+        return ph
+
+    one = fresh(None)
+    one.upload(pos, vel, mass, pinned)
+    one.step(dt, 11)
+    ref = one.download_state()
+    one.close()
+    a = fresh([0, 1])
+    a.upload(pos, vel, mass, pinned)
+    for _ in range(11):
+        a.step(dt, 1)                      # per-frame calls: speculative drifts in between
+    full = a.download_state()
+    info = a.partition_info()
+    a.close()
+    assert info["curve"] and info["partitions"] >= 3
+    assert np.abs(full[0] - ref[0]).max() <= 1e-10 * np.abs(ref[0]).max()
+    assert np.abs(full[1] - ref[1]).max() <= 1e-8 * np.abs(ref[1]).max()
+    assert np.abs(full[2] - ref[2]).max() <= 1e-6 * np.abs(ref[2]).max()
+    assert np.array_equal(full[0][pinned == 1], pos[pinned == 1])      # pins followed their bodies
+    # checkpoint after 5 frames (between the regroupings at generations 3 and 6 ...), resume, 6 more frames
+    b = fresh([0, 1])
+    b.upload(pos, vel, mass, pinned)
+    for _ in range(5):
+        b.step(dt, 1)
+    p, v, acc, _ = b.download_state()
+    order, age = b.stream_order()
+    b.close()
+    c = fresh([0, 1])
+    c.upload_state(p, v, acc if integ == 1 else None, mass, pinned)
+    c.set_stream_order(order, age)
+    for _ in range(6):
+        c.step(dt, 1)
+    resumed = c.download_state()
+    c.close()
+    for k in range(3):
+        assert np.array_equal(resumed[k], full[k]), k

@@ -504,11 +504,16 @@ def test_overlap_grid_equals_all_pairs_large(pkg, ph, dim, monkeypatch):
     assert ph.count_overlaps(np.zeros(n)) == (0, None)
 
 
+@pytest.mark.parametrize("resort", [None, "2"])
 @pytest.mark.parametrize("integ", [1, 0])
-def test_checkpoint_resume_is_bit_exact(pkg, tmp_path, integ):
+def test_checkpoint_resume_is_bit_exact(pkg, tmp_path, monkeypatch, integ, resort):
     """Snapshot to disk mid-run (download_state -> scenarios.save_snapshot), resume in a fresh context
     (load_snapshot -> upload_state): the resumed run equals the uninterrupted one bit for bit
-    (the reference keeps scenarios in memory only, Scenario.hpp:14-50; this is the resume it lacks)."""
+    (the reference keeps scenarios in memory only, Scenario.hpp:14-50; this is the resume it lacks).
+    resort = "2": the stream is re-sorted every 2 generations instead of 64, so the resumed run has to
+    re-sort at the same frames as the uninterrupted one (the checkpoint carries the age of the order)."""
+    if resort:
+        monkeypatch.setenv("NB_RESORT_EVERY", resort)
     n = 5000
     pos, vel, mass = pkg.scenarios.plummer(n, seed=31, dim=3)
     eps = 3.844e8 / np.sqrt(n)
