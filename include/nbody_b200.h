@@ -113,9 +113,9 @@ int nb_create_multi(const int* devices, int n_dev, nb_ctx** out);
 /* Devices behind a handle (1 for nb_create / nb_create_sharded contexts). */
 int nb_num_devices(nb_ctx* ctx);
 
-/* Target-partitioned context: rank `rank` of `world` owns bodies [lo,hi) of every upload
- * (nb_local_range) and exchanges packed positions with its peers through NCCL once per
- * force evaluation. `nccl_unique_id` is the 128-byte id from nb_comm_unique_id() on rank 0,
+/* Target-partitioned context: rank `rank` of `world` uploads and downloads rows [lo,hi) of the caller's
+ * arrays (nb_local_range), computes one P-th of the targets (nb_partition_info below says which) and
+ * exchanges packed positions with its peers through NCCL once per force evaluation. `nccl_unique_id` is the 128-byte id from nb_comm_unique_id() on rank 0,
  * distributed by the caller (torch.distributed / MPI / a file). Collective over all ranks. */
 int nb_comm_unique_id(void* out_id_128);
 int nb_create_sharded(int device, int rank, int world, const void* nccl_unique_id, nb_ctx** out);
@@ -167,7 +167,8 @@ int nb_download3(nb_ctx* ctx, double* pos_xyz, double* vel_xyz, double* acc_xyz)
 int nb_download_state(nb_ctx* ctx, int dim, double* pos, double* vel, double* acc, double* acc_prev);
 
 /* The order in which the FP32 path streams the bodies (a Hilbert-curve order of the positions at the last
- * sort; order[k] = body row at stream position k; a sharded context fills and reads its own rows only) and
+ * sort; order[k] = the caller's row of the body at stream position k; a sharded context fills and reads entries
+ * [lo,hi) only — stream positions, which in a multi-GPU context also say which GPU computes the body) and
  * the number of generations packed since that sort. The order fixes the summation order of every force sum,
  * so a checkpoint that must resume bit-identically carries both: nb_upload_state, then nb_set_stream_order.
  * The library re-sorts on its own every 64 generations (NB_RESORT_EVERY). */
@@ -184,8 +185,9 @@ int nb_partition_info(nb_ctx* ctx, int64_t* values);
 
 int64_t nb_num_bodies(nb_ctx* ctx);
 int nb_local_range(nb_ctx* ctx, int64_t* lo, int64_t* hi);
-/* The target partition a sharded context uses: contiguous, aligned to the 512-body source
- * tile, equal tile counts per rank (so the all-gather is uniform). Host-only, no context. */
+/* The row ranges of a multi-GPU context (the caller's rows a rank uploads / downloads, and the stretch of the
+ * stream it computes): contiguous, aligned to the 512-body source tile, equal tile counts per rank (so the
+ * all-gathers are uniform). Host-only, no context. */
 int nb_partition(int64_t n, int rank, int world, int64_t* lo, int64_t* hi);
 
 /* ---- the hot path ----------------------------------------------------------------- */
