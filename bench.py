@@ -212,6 +212,7 @@ def side_figure(pkg, device, pos, vel, mass, eps, dt, steps, env=None):
     p.set_config(softening=eps, integrator=1)
     p.upload(pos, vel, mass)
     p.step(dt, 3)
+    p.flush_l2()  # allocates the flush buffer outside the timed region
     p.synchronize()
     sampler = ClockSampler(device)
     sampler.start()
@@ -273,6 +274,7 @@ def run_ours(args):
     ph.step(dt, 1, diagnostics=True)  # first frame evaluates a(x0) like the gravity system, then one step
     e_first = ph.step_diagnostics().energy
     for _ in range(warm - 1):
+        ph.flush_l2()  # also allocates the 256 MiB flush buffer here, outside the timed region
         ph.step(dt, 1)
     barrier()
 
